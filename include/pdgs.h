@@ -1,0 +1,155 @@
+/* pdgs.h -- C ABI of the B200-native differentiable Gaussian-splat rasterizer (libpdgs.so).
+ *
+ * This is the drop-in boundary under the Python package `diff_gaussian_rasterization`.
+ * Each entry point names the reference interface it replaces.  The reference's native
+ * module is the pinned submodule graphdeco-inria/diff-gaussian-rasterization@9c5c2028
+ * (branch dr_aa), whose source is ABSENT from /root/reference (.SUBMODULES.json: "missing");
+ * the interface is therefore cited through its only caller,
+ * /root/reference/gaussian_renderer/__init__.py:14,36-52,104-112, and through SURVEY.md
+ * section 8(a)/(b) and Appendix B (upstream recall):
+ *
+ *   pdgs_forward       <- _C.rasterize_gaussians          (RasterizeGaussiansCUDA -> Rasterizer::forward)
+ *   pdgs_backward      <- _C.rasterize_gaussians_backward (RasterizeGaussiansBackwardCUDA -> Rasterizer::backward)
+ *   pdgs_mark_visible  <- _C.mark_visible                 (markVisible -> checkFrustum)
+ *   pdgs_*_bytes       <- the reference's resize-callback "required<State>(n)" sizing of
+ *                         geomBuffer / binningBuffer / imgBuffer
+ *   pdgs_sort_pairs    <- the cub::DeviceRadixSort::SortPairs call inside Rasterizer::forward
+ *                         (exposed so the sort stage can be tested and timed alone)
+ *
+ * Conventions: plain pointers and sizes, no torch types.  Every `const float*` / output
+ * pointer is a DEVICE pointer on the current CUDA device unless marked "host".  All work is
+ * enqueued on `stream`.  Matrices are the reference's transposed 4x4s (flat 4*c+r = (r,c),
+ * /root/reference/scene/cameras.py:86-88).  Functions return 0 or a negative PDGS_E_* code;
+ * pdgs_last_error() gives the message for the calling thread.
+ */
+#ifndef PDGS_H
+#define PDGS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PDGS_OK 0
+#define PDGS_NEED_BINNING 1      /* not an error: binning capacity too small, call again with resume=1 */
+#define PDGS_E_INVALID (-1)      /* bad argument (shape / null pointer / flag combination) */
+#define PDGS_E_CUDA (-2)         /* a CUDA call or kernel failed; see pdgs_last_error() */
+#define PDGS_E_OVERFLOW (-3)     /* number of (tile, Gaussian) pairs does not fit 2^30 */
+#define PDGS_E_NO_DEVICE (-4)    /* no usable sm_100 device / kernels missing for this device */
+
+typedef struct PdgsHandle PdgsHandle; /* per-thread/stream context: pinned counter slot, events */
+
+/* Camera + flags: the fields of GaussianRasterizationSettings
+ * (/root/reference/gaussian_renderer/__init__.py:36-50). */
+typedef struct PdgsCamera {
+  int32_t image_height, image_width;
+  float tanfovx, tanfovy;
+  const float* bg;          /* [3]  device */
+  float scale_modifier;
+  const float* viewmatrix;  /* [16] device */
+  const float* projmatrix;  /* [16] device */
+  int32_t sh_degree;        /* active degree 0..3 */
+  const float* campos;      /* [3]  device */
+  int32_t prefiltered;      /* accepted, ignored (culled points are simply skipped) */
+  int32_t debug;            /* 1: synchronise + check after every kernel */
+  int32_t antialiasing;
+} PdgsCamera;
+
+/* The Gaussians: arguments of GaussianRasterizer.forward
+ * (/root/reference/gaussian_renderer/__init__.py:104-112).  Exactly one of shs /
+ * colors_precomp and exactly one of (scales, rotations) / cov3D_precomp is non-NULL. */
+typedef struct PdgsScene {
+  int64_t P;                    /* number of Gaussians */
+  int32_t M;                    /* SH coefficients per Gaussian in `shs` (1,4,9,16); 0 if shs NULL */
+  const float* means3D;         /* [P,3] */
+  const float* shs;             /* [P,M,3] */
+  const float* colors_precomp;  /* [P,3] */
+  const float* opacities;       /* [P] */
+  const float* scales;          /* [P,3] */
+  const float* rotations;       /* [P,4] */
+  const float* cov3D_precomp;   /* [P,6] */
+} PdgsScene;
+
+/* Per-call state, allocated by the caller with the sizes below (the reference's
+ * geomBuffer / binningBuffer / imgBuffer).  It must stay alive until backward. */
+typedef struct PdgsState {
+  void* geom;    size_t geom_bytes;      /* pdgs_geom_bytes(P) */
+  void* image;   size_t image_bytes;     /* pdgs_image_bytes(W,H) */
+  void* binning; size_t binning_bytes;   /* pdgs_binning_bytes(capacity_pairs, P); may be NULL/0 */
+  int64_t capacity_pairs;                /* pairs the binning buffer was sized for */
+} PdgsState;
+
+typedef struct PdgsForwardOut {
+  float* color;      /* [3,H,W] */
+  float* invdepth;   /* [1,H,W] */
+  int32_t* radii;    /* [P] */
+} PdgsForwardOut;
+
+typedef struct PdgsGrads {       /* any pointer may be NULL = not wanted */
+  float* means3D;        /* [P,3] */
+  float* means2D;        /* [P,3] (.z = 0) */
+  float* shs;            /* [P,M,3] */
+  float* colors_precomp; /* [P,3] */
+  float* opacities;      /* [P] */
+  float* scales;         /* [P,3] */
+  float* rotations;      /* [P,4] */
+  float* cov3D_precomp;  /* [P,6] */
+  int32_t accumulate;    /* 0: overwrite (dense, zeros for culled); 1: += into the buffers */
+} PdgsGrads;
+
+const char* pdgs_last_error(void);
+const char* pdgs_version(void);
+
+int pdgs_create(PdgsHandle** out);
+int pdgs_destroy(PdgsHandle* h);
+
+size_t pdgs_geom_bytes(int64_t P);
+size_t pdgs_image_bytes(int32_t width, int32_t height);
+size_t pdgs_binning_bytes(int64_t capacity_pairs, int64_t P);
+size_t pdgs_backward_scratch_bytes(int64_t P);
+
+/* Forward.  resume=0: preprocess + scan, then (if state->capacity_pairs > 0) the binning,
+ * sort and blend are launched speculatively behind a device-side guard; the host waits only
+ * for the pair count.  Returns PDGS_OK when the image is complete (enqueued), or
+ * PDGS_NEED_BINNING with *num_rendered set when the binning buffer is absent/too small:
+ * allocate pdgs_binning_bytes(>= *num_rendered, P) and call again with resume=1, which runs
+ * only duplicateWithKeys -> sort -> ranges -> blend on the state already in `geom`. */
+int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, PdgsState* state,
+                 const PdgsForwardOut* out, int32_t resume, int64_t* num_rendered, void* stream);
+
+/* Backward.  dL_dinvdepth may be NULL (treated as zeros).  scratch: pdgs_backward_scratch_bytes(P). */
+int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, const PdgsState* state,
+                  const int32_t* radii, int64_t num_rendered, const float* dL_dcolor, const float* dL_dinvdepth,
+                  void* scratch, size_t scratch_bytes, const PdgsGrads* grads, void* stream);
+
+int pdgs_mark_visible(const float* means3D, const float* viewmatrix, const float* projmatrix, int64_t P,
+                      uint8_t* present, void* stream);
+
+/* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs over key bits [0, end_bit).
+ * scratch: pdgs_sort_scratch_bytes(n).  Result in keys_out / vals_out.  keys_in/vals_in are clobbered. */
+size_t pdgs_sort_scratch_bytes(int64_t n);
+int pdgs_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int64_t n,
+                    int32_t end_bit, void* scratch, size_t scratch_bytes, void* stream);
+
+/* Read-only views into the saved state, for parity tests (device pointers, valid until the
+ * state buffers are freed). */
+typedef struct PdgsStateView {
+  const uint32_t* point_list;   /* [R] sorted Gaussian ids */
+  const uint64_t* sorted_keys;  /* [R] (tile << 32) | depth bits */
+  const uint32_t* ranges;       /* [T,2] */
+  const float* final_T;         /* [H*W] */
+  const uint32_t* n_contrib;    /* [H*W] */
+  const uint32_t* tiles_touched;/* [P] */
+  const uint32_t* point_offsets;/* [P] inclusive scan */
+  const float* xy;              /* [P,4] (x, y, conic.x, conic.y) */
+  const float* conic_opacity;   /* [P,4] (conic.z, opacity, 1/depth, depth) */
+  const float* rgb;             /* [P,4] (r, g, b, clamped-bits) */
+} PdgsStateView;
+int pdgs_state_view(const PdgsState* state, int64_t P, int32_t width, int32_t height, PdgsStateView* view);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDGS_H */

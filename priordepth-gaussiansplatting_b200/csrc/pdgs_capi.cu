@@ -1,0 +1,269 @@
+// C ABI of libpdgs.so (declared in include/pdgs.h) and the host-side orchestration that
+// plays the role of the reference's rasterize_points.cu + rasterizer_impl.cu (source absent;
+// SURVEY.md section 8(a) rows a5/a6, Appendix A.1).  Differences by design:
+//   * no blocking device->host copy in the middle of forward: the binning/sort/blend kernels
+//     are enqueued speculatively behind a device-side capacity guard and the host waits only
+//     for the 8-byte pair count (event after the scan);
+//   * everything runs on the caller's stream;
+//   * no CPU fallback of any kind: without a CUDA device every entry point fails.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/pdgs.h"
+#include "pdgs_internal.cuh"
+
+using namespace pdgs;
+
+struct PdgsHandle {
+  int device;
+  unsigned long long* host_slot;  // pinned: [0] = num_rendered | overflow << 32
+  cudaEvent_t ev;
+};
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, const char* detail = "") {
+  snprintf(g_err, sizeof(g_err), fmt, detail);
+  return code;
+}
+#define PD_CUDA(call)                                                        \
+  do {                                                                       \
+    cudaError_t _e = (call);                                                 \
+    if (_e != cudaSuccess) {                                                 \
+      snprintf(g_err, sizeof(g_err), "%s failed: %s", #call, cudaGetErrorString(_e)); \
+      return PDGS_E_CUDA;                                                    \
+    }                                                                        \
+  } while (0)
+
+extern "C" {
+
+const char* pdgs_last_error(void) { return g_err; }
+const char* pdgs_version(void) { return "pdgs-b200 0.1 (sm_100a)"; }
+
+int pdgs_create(PdgsHandle** out) {
+  if (!out) return fail(PDGS_E_INVALID, "pdgs_create: out is NULL");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return fail(PDGS_E_NO_DEVICE, "pdgs_create: no CUDA device (this library has no CPU path)");
+  }
+  PdgsHandle* h = new PdgsHandle();
+  PD_CUDA(cudaGetDevice(&h->device));
+  cudaDeviceProp prop;
+  PD_CUDA(cudaGetDeviceProperties(&prop, h->device));
+  if (prop.major != 10) {
+    delete h;
+    return fail(PDGS_E_NO_DEVICE, "pdgs_create: device is not sm_100 (kernels are built for sm_100a only)");
+  }
+  PD_CUDA(cudaHostAlloc((void**)&h->host_slot, 64, cudaHostAllocDefault));
+  PD_CUDA(cudaEventCreateWithFlags(&h->ev, cudaEventDisableTiming));
+  *out = h;
+  return PDGS_OK;
+}
+
+int pdgs_destroy(PdgsHandle* h) {
+  if (!h) return PDGS_OK;
+  cudaFreeHost(h->host_slot);
+  cudaEventDestroy(h->ev);
+  delete h;
+  return PDGS_OK;
+}
+
+size_t pdgs_geom_bytes(int64_t P) { return carve_geom(nullptr, P).bytes; }
+size_t pdgs_image_bytes(int32_t width, int32_t height) { return carve_image(nullptr, width, height).bytes; }
+size_t pdgs_binning_bytes(int64_t capacity_pairs, int64_t P) {
+  (void)P;
+  return carve_binning(nullptr, capacity_pairs).bytes;
+}
+size_t pdgs_backward_scratch_bytes(int64_t P) { return align_up((size_t)(P > 0 ? P : 1) * ACC_FLOATS * sizeof(float)); }
+size_t pdgs_sort_scratch_bytes(int64_t n) { return carve_sort_scratch(nullptr, n).bytes + 256; }
+
+static bool aligned16(const void* p) { return (((uintptr_t)p) & 15u) == 0; }
+
+static int make_args(const PdgsScene* sc, const PdgsCamera* cam, DeviceArgs& a) {
+  if (!sc || !cam) return fail(PDGS_E_INVALID, "scene/camera is NULL");
+  if (sc->P < 0) return fail(PDGS_E_INVALID, "P < 0");
+  if (cam->image_width <= 0 || cam->image_height <= 0) return fail(PDGS_E_INVALID, "image size must be positive");
+  if (sc->P > 0) {
+    if (!sc->means3D || !sc->opacities) return fail(PDGS_E_INVALID, "means3D/opacities is NULL");
+    if ((sc->shs != nullptr) == (sc->colors_precomp != nullptr))
+      return fail(PDGS_E_INVALID, "exactly one of shs / colors_precomp must be given");
+    const bool sr = sc->scales != nullptr && sc->rotations != nullptr;
+    if (sr == (sc->cov3D_precomp != nullptr) || ((sc->scales != nullptr) != (sc->rotations != nullptr)))
+      return fail(PDGS_E_INVALID, "exactly one of (scales, rotations) / cov3D_precomp must be given");
+    if (sc->shs && (sc->M < 1 || sc->M > 16)) return fail(PDGS_E_INVALID, "SH coefficient count M must be in 1..16");
+    if (sc->shs && (cam->sh_degree < 0 || cam->sh_degree > 3 || (cam->sh_degree + 1) * (cam->sh_degree + 1) > sc->M))
+      return fail(PDGS_E_INVALID, "sh_degree needs more coefficients than shs holds (or is outside 0..3)");
+    if (sc->rotations && !aligned16(sc->rotations)) return fail(PDGS_E_INVALID, "rotations must be 16-byte aligned");
+    if (sc->shs && sc->M == 16 && !aligned16(sc->shs)) return fail(PDGS_E_INVALID, "shs must be 16-byte aligned");
+  }
+  if (!cam->viewmatrix || !cam->projmatrix || !cam->bg) return fail(PDGS_E_INVALID, "viewmatrix/projmatrix/bg is NULL");
+  if (sc->shs && !cam->campos) return fail(PDGS_E_INVALID, "campos is NULL");
+  a.means3D = sc->means3D; a.shs = sc->shs; a.colors_precomp = sc->colors_precomp; a.opacities = sc->opacities;
+  a.scales = sc->scales; a.rotations = sc->rotations; a.cov3D_precomp = sc->cov3D_precomp;
+  a.viewmatrix = cam->viewmatrix; a.projmatrix = cam->projmatrix; a.campos = cam->campos; a.bg = cam->bg;
+  a.P = sc->P; a.M = sc->shs ? sc->M : 0;
+  a.tanfovx = cam->tanfovx; a.tanfovy = cam->tanfovy;
+  a.W = cam->image_width; a.H = cam->image_height;
+  a.focal_x = (float)a.W / (2.0f * cam->tanfovx);
+  a.focal_y = (float)a.H / (2.0f * cam->tanfovy);
+  a.scale_modifier = cam->scale_modifier;
+  a.grid_x = (a.W + TILE - 1) / TILE; a.grid_y = (a.H + TILE - 1) / TILE;
+  a.sh_degree = cam->sh_degree; a.antialiasing = cam->antialiasing ? 1 : 0;
+  return PDGS_OK;
+}
+
+#define PD_STEP(dbg, s, call)                                                                         \
+  do {                                                                                                \
+    PD_CUDA(call);                                                                                    \
+    if (dbg) {                                                                                        \
+      cudaError_t _e = cudaStreamSynchronize(s);                                                      \
+      if (_e != cudaSuccess) {                                                                        \
+        snprintf(g_err, sizeof(g_err), "debug: kernel behind %s failed: %s", #call, cudaGetErrorString(_e)); \
+        return PDGS_E_CUDA;                                                                           \
+      }                                                                                               \
+    }                                                                                                 \
+  } while (0)
+
+static int run_binning_and_blend(const DeviceArgs& a, GeomView g, ImageView im, PdgsState* st, const int32_t* radii,
+                                 const PdgsForwardOut* out, int debug, cudaStream_t s) {
+  BinningView b = carve_binning(st->binning, st->capacity_pairs);
+  if (b.bytes > st->binning_bytes) return fail(PDGS_E_INVALID, "binning buffer smaller than pdgs_binning_bytes(capacity)");
+  const int tiles = a.grid_x * a.grid_y;
+  const int npass = num_sort_passes(tiles);
+  uint64_t* kin = (npass % 2 == 0) ? b.keys_a : b.keys_b;
+  uint32_t* vin = (npass % 2 == 0) ? b.point_list : b.vals_b;
+  PD_STEP(debug, s, launch_duplicate(a, g, radii, kin, vin, st->capacity_pairs, s));
+  PD_STEP(debug, s, launch_sort(b.keys_a, b.point_list, b.keys_b, b.vals_b, &g.ctrl->num_rendered, st->capacity_pairs,
+                                npass, b.sort_scratch, s));
+  PD_STEP(debug, s, launch_ranges(b.keys_a, &g.ctrl->num_rendered, st->capacity_pairs, im.ranges, tiles, s));
+  PD_STEP(debug, s, launch_render_forward(a, g, im, b.point_list, st->capacity_pairs, out->color, out->invdepth, s));
+  return PDGS_OK;
+}
+
+int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, PdgsState* state,
+                 const PdgsForwardOut* out, int32_t resume, int64_t* num_rendered, void* stream) {
+  if (!h || !state || !out || !num_rendered) return fail(PDGS_E_INVALID, "pdgs_forward: NULL argument");
+  DeviceArgs a;
+  int rc = make_args(scene, cam, a);
+  if (rc != PDGS_OK) return rc;
+  if (!out->color || !out->invdepth || (a.P > 0 && !out->radii)) return fail(PDGS_E_INVALID, "output pointer is NULL");
+  if (!state->geom || state->geom_bytes < pdgs_geom_bytes(a.P)) return fail(PDGS_E_INVALID, "geom buffer too small");
+  if (!state->image || state->image_bytes < pdgs_image_bytes(a.W, a.H)) return fail(PDGS_E_INVALID, "image buffer too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  GeomView g = carve_geom(state->geom, a.P);
+  ImageView im = carve_image(state->image, a.W, a.H);
+  const int debug = cam->debug;
+  const bool have_binning = state->binning != nullptr && state->capacity_pairs > 0;
+
+  if (!resume) {
+    PD_CUDA(cudaMemsetAsync(g.ctrl, 0, sizeof(Ctrl), s));
+    PD_CUDA(cudaMemsetAsync(g.scan_state, 0, ((size_t)(a.P > 0 ? a.P : 1) + SCAN_TILE - 1) / SCAN_TILE * 8, s));
+    PD_STEP(debug, s, launch_preprocess(a, g, out->radii, s));
+    PD_STEP(debug, s, launch_scan(g, a.P, s));
+    PD_CUDA(cudaMemcpyAsync(h->host_slot, g.ctrl, 8, cudaMemcpyDeviceToHost, s));
+    PD_CUDA(cudaEventRecord(h->ev, s));
+    if (have_binning) {
+      rc = run_binning_and_blend(a, g, im, state, out->radii, out, debug, s);
+      if (rc != PDGS_OK) return rc;
+    }
+    PD_CUDA(cudaEventSynchronize(h->ev));
+    const unsigned long long slot = h->host_slot[0];
+    const uint32_t R = (uint32_t)(slot & 0xffffffffull);
+    const uint32_t ovf = (uint32_t)(slot >> 32);
+    *num_rendered = (int64_t)R;
+    if (ovf) return fail(PDGS_E_OVERFLOW, "number of (tile, Gaussian) pairs >= 2^30");
+    if (!have_binning || (int64_t)R > state->capacity_pairs) return PDGS_NEED_BINNING;
+    return PDGS_OK;
+  }
+  // resume: geometry state is valid, R known; (re)run binning + blend with a big-enough buffer
+  if (!have_binning) return fail(PDGS_E_INVALID, "resume without a binning buffer");
+  if (*num_rendered > state->capacity_pairs) return fail(PDGS_E_INVALID, "resume: capacity < num_rendered");
+  return run_binning_and_blend(a, g, im, state, out->radii, out, debug, s);
+}
+
+int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, const PdgsState* state,
+                  const int32_t* radii, int64_t num_rendered, const float* dL_dcolor, const float* dL_dinvdepth,
+                  void* scratch, size_t scratch_bytes, const PdgsGrads* grads, void* stream) {
+  if (!h || !state || !grads || !dL_dcolor) return fail(PDGS_E_INVALID, "pdgs_backward: NULL argument");
+  DeviceArgs a;
+  int rc = make_args(scene, cam, a);
+  if (rc != PDGS_OK) return rc;
+  if (a.P == 0) return PDGS_OK;
+  if (!radii) return fail(PDGS_E_INVALID, "radii is NULL");
+  if (!scratch || scratch_bytes < pdgs_backward_scratch_bytes(a.P)) return fail(PDGS_E_INVALID, "backward scratch too small");
+  if (grads->rotations && !aligned16(grads->rotations)) return fail(PDGS_E_INVALID, "grad rotations must be 16-byte aligned");
+  if (grads->shs && a.M == 16 && !aligned16(grads->shs)) return fail(PDGS_E_INVALID, "grad shs must be 16-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  GeomView g = carve_geom(state->geom, a.P);
+  ImageView im = carve_image(state->image, a.W, a.H);
+  const int debug = cam->debug;
+  float* acc = (float*)scratch;
+  PD_CUDA(cudaMemsetAsync(acc, 0, (size_t)a.P * ACC_FLOATS * sizeof(float), s));
+  if (num_rendered > 0) {
+    if (!state->binning) return fail(PDGS_E_INVALID, "binning buffer is NULL");
+    BinningView b = carve_binning(state->binning, state->capacity_pairs);
+    PD_STEP(debug, s, launch_render_backward(a, g, im, b.point_list, dL_dcolor, dL_dinvdepth, acc, s));
+  }
+  GradPtrs gp;
+  gp.means3D = grads->means3D; gp.means2D = grads->means2D; gp.shs = grads->shs;
+  gp.colors_precomp = grads->colors_precomp; gp.opacities = grads->opacities; gp.scales = grads->scales;
+  gp.rotations = grads->rotations; gp.cov3D_precomp = grads->cov3D_precomp; gp.accumulate = grads->accumulate;
+  PD_STEP(debug, s, launch_preprocess_backward(a, g, radii, acc, gp, s));
+  return PDGS_OK;
+}
+
+int pdgs_mark_visible(const float* means3D, const float* viewmatrix, const float* projmatrix, int64_t P,
+                      uint8_t* present, void* stream) {
+  (void)projmatrix;
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return fail(PDGS_E_INVALID, "pdgs_mark_visible: bad argument");
+  PD_CUDA(launch_mark_visible(means3D, viewmatrix, P, present, (cudaStream_t)stream));
+  return PDGS_OK;
+}
+
+int pdgs_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int64_t n,
+                    int32_t end_bit, void* scratch, size_t scratch_bytes, void* stream) {
+  if (n < 0 || end_bit < 1 || end_bit > 64) return fail(PDGS_E_INVALID, "pdgs_sort_pairs: bad n / end_bit");
+  if (n == 0) return PDGS_OK;
+  if ((uint64_t)n >= MAX_PAIRS) return fail(PDGS_E_OVERFLOW, "pdgs_sort_pairs: n >= 2^30");
+  if (!keys_in || !vals_in || !keys_out || !vals_out || !scratch || scratch_bytes < pdgs_sort_scratch_bytes(n))
+    return fail(PDGS_E_INVALID, "pdgs_sort_pairs: NULL buffer or scratch too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int npass = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
+  // the count lives in the last 256 bytes of the scratch
+  SortScratch sc = carve_sort_scratch(scratch, n);
+  uint32_t* cnt = (uint32_t*)((char*)scratch + sc.bytes);
+  const uint32_t n32 = (uint32_t)n;
+  PD_CUDA(cudaMemcpyAsync(cnt, &n32, 4, cudaMemcpyHostToDevice, s));
+  if (npass % 2 == 0) {
+    // input must sit in A (= out buffers) for an even number of passes: copy in -> out first
+    PD_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, s));
+    PD_CUDA(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+  }
+  PD_CUDA(launch_sort(keys_out, vals_out, keys_in, vals_in, cnt, n, npass, scratch, s));
+  return PDGS_OK;
+}
+
+int pdgs_state_view(const PdgsState* state, int64_t P, int32_t width, int32_t height, PdgsStateView* view) {
+  if (!state || !view) return fail(PDGS_E_INVALID, "pdgs_state_view: NULL argument");
+  GeomView g = carve_geom(state->geom, P);
+  ImageView im = carve_image(state->image, width, height);
+  memset(view, 0, sizeof(*view));
+  if (state->binning) {
+    BinningView b = carve_binning(state->binning, state->capacity_pairs);
+    view->point_list = b.point_list;
+    view->sorted_keys = b.keys_a;
+  }
+  view->ranges = (const uint32_t*)im.ranges;
+  view->final_T = im.final_T;
+  view->n_contrib = im.n_contrib;
+  view->tiles_touched = g.tiles_touched;
+  view->point_offsets = g.point_offsets;
+  view->xy = (const float*)g.gA;
+  view->conic_opacity = (const float*)g.gB;
+  view->rgb = (const float*)g.gC;
+  return PDGS_OK;
+}
+
+}  // extern "C"

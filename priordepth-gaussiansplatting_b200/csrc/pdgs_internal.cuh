@@ -1,0 +1,182 @@
+// Internal layout of the per-call state blobs and the launch functions shared
+// between translation units of libpdgs.so.  The blobs play the role of the
+// reference's geomBuffer / binningBuffer / imgBuffer but the
+// layout is SoA float4 records sized for coalesced 16-byte gathers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include "pdgs_math.cuh"
+
+namespace pdgs {
+
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int MAX_PASSES = 8;
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 12;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 3072 pairs per CTA
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 16;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;  // 4096 counts per CTA
+constexpr uint32_t MAX_PAIRS = 1u << 30;               // look-back words carry 30-bit counts
+
+// Control block at the start of the geometry blob (device memory, 256 B).
+struct Ctrl {
+  uint32_t num_rendered;  // R = sum of tiles_touched
+  uint32_t overflow;      // R >= 2^30
+  uint32_t scan_ticket;
+  uint32_t error;
+  uint32_t sort_ticket[MAX_PASSES];
+  uint32_t pad[52];
+};
+static_assert(sizeof(Ctrl) == 256, "Ctrl must be 256 bytes");
+
+inline __host__ __device__ size_t align_up(size_t v, size_t a = 128) { return (v + a - 1) / a * a; }
+
+struct GeomView {
+  Ctrl* ctrl;
+  float4* gA;               // (x, y, conic.x, conic.y)
+  float4* gB;               // (conic.z, opacity*h, 1/depth, depth)
+  float4* gC;               // (r, g, b, clamped bits)
+  uint32_t* tiles_touched;  // [P]
+  uint32_t* point_offsets;  // [P] inclusive scan
+  unsigned long long* scan_state;  // [ceil(P/SCAN_TILE)]
+  size_t bytes;
+};
+
+inline __host__ GeomView carve_geom(void* base, int64_t P) {
+  GeomView v;
+  char* p = (char*)base;
+  size_t off = 0;
+  const size_t Pn = (size_t)(P > 0 ? P : 1);
+  v.ctrl = (Ctrl*)(p + off); off += align_up(sizeof(Ctrl));
+  v.gA = (float4*)(p + off); off += align_up(Pn * sizeof(float4));
+  v.gB = (float4*)(p + off); off += align_up(Pn * sizeof(float4));
+  v.gC = (float4*)(p + off); off += align_up(Pn * sizeof(float4));
+  v.tiles_touched = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
+  v.point_offsets = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
+  const size_t nscan = (Pn + SCAN_TILE - 1) / SCAN_TILE;
+  v.scan_state = (unsigned long long*)(p + off); off += align_up(nscan * sizeof(unsigned long long));
+  v.bytes = off;
+  return v;
+}
+
+struct ImageView {
+  uint2* ranges;        // [tiles]
+  float* final_T;       // [H*W]
+  uint32_t* n_contrib;  // [H*W]
+  size_t bytes;
+};
+
+inline __host__ ImageView carve_image(void* base, int W, int H) {
+  ImageView v;
+  char* p = (char*)base;
+  size_t off = 0;
+  const size_t tiles = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+  const size_t hw = (size_t)W * H;
+  v.ranges = (uint2*)(p + off); off += align_up(tiles * sizeof(uint2));
+  v.final_T = (float*)(p + off); off += align_up(hw * sizeof(float));
+  v.n_contrib = (uint32_t*)(p + off); off += align_up(hw * sizeof(uint32_t));
+  v.bytes = off;
+  return v;
+}
+
+struct SortScratch {
+  uint32_t* hist;      // [MAX_PASSES][RADIX] global digit histograms
+  uint32_t* tickets;   // [MAX_PASSES]
+  uint32_t* lookback;  // [MAX_PASSES][ntiles][RADIX]
+  size_t ntiles;
+  size_t bytes;        // whole scratch
+  size_t zero_bytes;   // prefix that must be zeroed before a sort
+};
+
+inline __host__ SortScratch carve_sort_scratch(void* base, int64_t capacity) {
+  SortScratch s;
+  char* p = (char*)base;
+  size_t off = 0;
+  const size_t cap = (size_t)(capacity > 0 ? capacity : 1);
+  s.ntiles = (cap + SORT_TILE - 1) / SORT_TILE;
+  s.hist = (uint32_t*)(p + off); off += align_up(MAX_PASSES * RADIX * sizeof(uint32_t));
+  s.tickets = (uint32_t*)(p + off); off += align_up(MAX_PASSES * sizeof(uint32_t));
+  s.lookback = (uint32_t*)(p + off); off += align_up((size_t)MAX_PASSES * s.ntiles * RADIX * sizeof(uint32_t));
+  s.bytes = off;
+  s.zero_bytes = off;
+  return s;
+}
+
+struct BinningView {
+  uint32_t* point_list;  // [cap] sorted Gaussian ids (buffer A values)
+  uint64_t* keys_a;      // [cap] sorted keys (buffer A)
+  uint64_t* keys_b;      // [cap]
+  uint32_t* vals_b;      // [cap]
+  void* sort_scratch;
+  size_t sort_scratch_bytes;
+  size_t bytes;
+};
+
+inline __host__ BinningView carve_binning(void* base, int64_t capacity) {
+  BinningView v;
+  char* p = (char*)base;
+  size_t off = 0;
+  const size_t cap = (size_t)(capacity > 0 ? capacity : 1);
+  v.point_list = (uint32_t*)(p + off); off += align_up(cap * sizeof(uint32_t));
+  v.keys_a = (uint64_t*)(p + off); off += align_up(cap * sizeof(uint64_t));
+  v.keys_b = (uint64_t*)(p + off); off += align_up(cap * sizeof(uint64_t));
+  v.vals_b = (uint32_t*)(p + off); off += align_up(cap * sizeof(uint32_t));
+  SortScratch s = carve_sort_scratch(nullptr, capacity);
+  v.sort_scratch = (void*)(p + off);
+  v.sort_scratch_bytes = s.bytes;
+  off += align_up(s.bytes);
+  v.bytes = off;
+  return v;
+}
+
+// Per-Gaussian gradient accumulator written by the backward blend (12 floats, 3 x float4):
+//   [0..3]  dmean2D.x, dmean2D.y, dconic.x, dconic.y
+//   [4..7]  dconic.w, dopacity, dinvdepth, -
+//   [8..11] dr, dg, db, -
+constexpr int ACC_FLOATS = 12;
+
+// ---- launchers (each enqueues on `stream`; returns cudaGetLastError()) ----
+struct DeviceArgs {
+  const float* means3D; const float* shs; const float* colors_precomp; const float* opacities;
+  const float* scales; const float* rotations; const float* cov3D_precomp;
+  const float* viewmatrix; const float* projmatrix; const float* campos; const float* bg;
+  int64_t P; int M;
+  float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
+  int W, H, grid_x, grid_y, sh_degree, antialiasing;
+};
+
+cudaError_t launch_preprocess(const DeviceArgs& a, GeomView g, int32_t* radii, cudaStream_t s);
+cudaError_t launch_scan(GeomView g, int64_t P, cudaStream_t s);
+cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, const int32_t* radii, uint64_t* keys, uint32_t* vals,
+                             int64_t capacity, cudaStream_t s);
+// Sorts pairs (keys_a, vals_a) <-> (keys_b, vals_b); input must sit in A if npass is even, in B if odd;
+// the result always lands in A.  n is read from *n_dev and must be <= capacity.
+cudaError_t launch_sort(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, const uint32_t* n_dev,
+                        int64_t capacity, int npass, void* scratch, cudaStream_t s);
+cudaError_t launch_ranges(const uint64_t* keys, const uint32_t* n_dev, int64_t capacity, uint2* ranges, int tiles,
+                          cudaStream_t s);
+cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
+                                  int64_t capacity, float* out_color, float* out_invdepth, cudaStream_t s);
+cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
+                                   const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s);
+struct GradPtrs {
+  float* means3D; float* means2D; float* shs; float* colors_precomp; float* opacities; float* scales;
+  float* rotations; float* cov3D_precomp; int accumulate;
+};
+cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const int32_t* radii, const float* acc,
+                                       GradPtrs gp, cudaStream_t s);
+cudaError_t launch_mark_visible(const float* means3D, const float* viewmatrix, int64_t P, uint8_t* present,
+                                cudaStream_t s);
+
+inline int num_sort_passes(int tiles) {
+  int bits = 0;
+  while ((1 << bits) <= tiles && bits < 31) ++bits;  // index of MSB + 1 (256 -> 9)
+  int total = 32 + bits;
+  return (total + RADIX_BITS - 1) / RADIX_BITS;
+}
+
+}  // namespace pdgs

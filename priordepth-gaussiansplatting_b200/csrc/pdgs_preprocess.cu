@@ -1,0 +1,283 @@
+// K1 preprocess (forward), fused K8+K9 preprocess backward, K10 mark_visible.
+// Replaces preprocessCUDA / computeCov2DCUDA-backward / preprocessCUDA-backward / checkFrustum
+// of the reference rasterizer (source absent).
+#include "pdgs_internal.cuh"
+
+namespace pdgs {
+
+namespace {
+
+constexpr int PRE_THREADS = 256;
+
+__device__ __forceinline__ void load_camera(const DeviceArgs& a, Camera* cam) {
+  // one CTA-wide cooperative load of the 35 camera floats into shared memory
+  const int t = threadIdx.x;
+  if (t < 16) cam->vm[t] = __ldg(a.viewmatrix + t);
+  else if (t < 32) cam->pm[t - 16] = __ldg(a.projmatrix + (t - 16));
+  else if (t < 35) cam->campos[t - 32] = a.campos ? __ldg(a.campos + (t - 32)) : 0.f;
+  else if (t == 35) {
+    cam->tanfovx = a.tanfovx; cam->tanfovy = a.tanfovy;
+    cam->focal_x = a.focal_x; cam->focal_y = a.focal_y;
+    cam->scale_modifier = a.scale_modifier;
+    cam->W = a.W; cam->H = a.H; cam->grid_x = a.grid_x; cam->grid_y = a.grid_y;
+    cam->sh_degree = a.sh_degree; cam->antialiasing = a.antialiasing;
+  }
+  __syncthreads();
+}
+
+struct ShGlobal {  // per-Gaussian SH block read through the read-only path
+  const float* p;
+  __device__ __forceinline__ float operator()(int i) const { return __ldg(p + i); }
+};
+
+struct ShRegs {  // SH block held in registers (48 floats, loaded as 12 x float4)
+  float v[48];
+  __device__ __forceinline__ float operator()(int i) const { return v[i]; }
+};
+
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(DeviceArgs a, GeomView g, int32_t* __restrict__ radii) {
+  __shared__ Camera cam;
+  load_camera(a, &cam);
+  const int64_t idx = (int64_t)blockIdx.x * PRE_THREADS + threadIdx.x;
+  if (idx >= a.P) return;
+  const float mx = __ldg(a.means3D + 3 * idx), my = __ldg(a.means3D + 3 * idx + 1), mz = __ldg(a.means3D + 3 * idx + 2);
+  float cov[6];
+  if (a.cov3D_precomp) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) cov[k] = __ldg(a.cov3D_precomp + 6 * idx + k);
+  } else {
+    const float sc[3] = {__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2)};
+    const float4 q4 = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+    const float q[4] = {q4.x, q4.y, q4.z, q4.w};
+    cov3d_from_scale_rot(sc, cam.scale_modifier, q, cov);
+  }
+  GeomOut go;
+  const bool vis = forward_geometry(cam, mx, my, mz, cov, go);
+  if (!vis) {
+    radii[idx] = 0;
+    g.tiles_touched[idx] = 0;
+    return;
+  }
+  float rgb[3];
+  unsigned clamped = 0;
+  if (a.colors_precomp) {
+    rgb[0] = __ldg(a.colors_precomp + 3 * idx);
+    rgb[1] = __ldg(a.colors_precomp + 3 * idx + 1);
+    rgb[2] = __ldg(a.colors_precomp + 3 * idx + 2);
+  } else {
+    const float dx = mx - cam.campos[0], dy = my - cam.campos[1], dz = mz - cam.campos[2];
+    if (a.M == 16) {
+      ShRegs sh;
+      const float4* src = reinterpret_cast<const float4*>(a.shs + (size_t)idx * 48);
+#pragma unroll
+      for (int k = 0; k < 12; ++k) {
+        const float4 v = __ldg(src + k);
+        sh.v[4 * k] = v.x; sh.v[4 * k + 1] = v.y; sh.v[4 * k + 2] = v.z; sh.v[4 * k + 3] = v.w;
+      }
+      clamped = sh_to_rgb(cam.sh_degree, dx, dy, dz, sh, rgb);
+    } else {
+      ShGlobal sh{a.shs + (size_t)idx * a.M * 3};
+      clamped = sh_to_rgb(cam.sh_degree, dx, dy, dz, sh, rgb);
+    }
+  }
+  const float opacity = __ldg(a.opacities + idx);
+  g.gA[idx] = make_float4(go.px, go.py, go.conA, go.conB);
+  g.gB[idx] = make_float4(go.conC, opacity * go.h, PD_DIV(1.0f, go.depth), go.depth);
+  g.gC[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
+  radii[idx] = go.radius;
+  g.tiles_touched[idx] = (uint32_t)((go.rx1 - go.rx0) * (go.ry1 - go.ry0));
+}
+
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(DeviceArgs a, GeomView g,
+                                                                        const int32_t* __restrict__ radii,
+                                                                        const float* __restrict__ acc, GradPtrs gp) {
+  __shared__ Camera cam;
+  load_camera(a, &cam);
+  const int64_t idx = (int64_t)blockIdx.x * PRE_THREADS + threadIdx.x;
+  if (idx >= a.P) return;
+  const bool vis = radii[idx] > 0;
+  const int M = a.M;
+  if (!vis) {
+    if (!gp.accumulate) {  // dense zero rows for culled Gaussians
+      if (gp.means3D) { gp.means3D[3 * idx] = 0.f; gp.means3D[3 * idx + 1] = 0.f; gp.means3D[3 * idx + 2] = 0.f; }
+      if (gp.means2D) { gp.means2D[3 * idx] = 0.f; gp.means2D[3 * idx + 1] = 0.f; gp.means2D[3 * idx + 2] = 0.f; }
+      if (gp.opacities) gp.opacities[idx] = 0.f;
+      if (gp.colors_precomp) { gp.colors_precomp[3 * idx] = 0.f; gp.colors_precomp[3 * idx + 1] = 0.f; gp.colors_precomp[3 * idx + 2] = 0.f; }
+      if (gp.scales) { gp.scales[3 * idx] = 0.f; gp.scales[3 * idx + 1] = 0.f; gp.scales[3 * idx + 2] = 0.f; }
+      if (gp.rotations) reinterpret_cast<float4*>(gp.rotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (gp.cov3D_precomp) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) gp.cov3D_precomp[6 * idx + k] = 0.f;
+      }
+      if (gp.shs) {
+        if (M == 16) {
+          float4* dst = reinterpret_cast<float4*>(gp.shs + (size_t)idx * 48);
+#pragma unroll
+          for (int k = 0; k < 12; ++k) dst[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+          for (int k = 0; k < 3 * M; ++k) gp.shs[(size_t)idx * 3 * M + k] = 0.f;
+        }
+      }
+    }
+    return;
+  }
+  const float4 a0 = __ldg(reinterpret_cast<const float4*>(acc) + 3 * idx);
+  const float4 a1 = __ldg(reinterpret_cast<const float4*>(acc) + 3 * idx + 1);
+  const float4 a2 = __ldg(reinterpret_cast<const float4*>(acc) + 3 * idx + 2);
+  const float4 gC = g.gC[idx];
+  BwdIn in;
+  in.g_mean2d_x = a0.x; in.g_mean2d_y = a0.y;
+  in.g_conic_x = a0.z; in.g_conic_y = a0.w; in.g_conic_w = a1.x;
+  in.g_opacity = a1.y; in.g_invdepth = a1.z;
+  in.g_rgb[0] = a2.x; in.g_rgb[1] = a2.y; in.g_rgb[2] = a2.z;
+  in.clamped = __float_as_uint(gC.w);
+
+  const float mx = __ldg(a.means3D + 3 * idx), my = __ldg(a.means3D + 3 * idx + 1), mz = __ldg(a.means3D + 3 * idx + 2);
+  float cov[6];
+  float sc[3] = {0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f};
+  if (a.cov3D_precomp) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) cov[k] = __ldg(a.cov3D_precomp + 6 * idx + k);
+  } else {
+    sc[0] = __ldg(a.scales + 3 * idx); sc[1] = __ldg(a.scales + 3 * idx + 1); sc[2] = __ldg(a.scales + 3 * idx + 2);
+    const float4 q4 = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+    q[0] = q4.x; q[1] = q4.y; q[2] = q4.z; q[3] = q4.w;
+    cov3d_from_scale_rot(sc, cam.scale_modifier, q, cov);
+  }
+  const float opacity = __ldg(a.opacities + idx);
+  float g_mean[3], g_op, g_cov[6];
+  geometry_backward(cam, mx, my, mz, cov, opacity, in, g_mean, g_op, g_cov);
+
+  // colour
+  if (a.colors_precomp) {
+    if (gp.colors_precomp) {
+      if (gp.accumulate) {
+        gp.colors_precomp[3 * idx] += in.g_rgb[0]; gp.colors_precomp[3 * idx + 1] += in.g_rgb[1]; gp.colors_precomp[3 * idx + 2] += in.g_rgb[2];
+      } else {
+        gp.colors_precomp[3 * idx] = in.g_rgb[0]; gp.colors_precomp[3 * idx + 1] = in.g_rgb[1]; gp.colors_precomp[3 * idx + 2] = in.g_rgb[2];
+      }
+    }
+  } else {
+    float grgb[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) grgb[c] = ((in.clamped >> c) & 1u) ? 0.f : in.g_rgb[c];
+    const float dx = mx - cam.campos[0], dy = my - cam.campos[1], dz = mz - cam.campos[2];
+    float gdir[3], basis[16];
+    if (M == 16) {
+      ShRegs sh;
+      const float4* src = reinterpret_cast<const float4*>(a.shs + (size_t)idx * 48);
+#pragma unroll
+      for (int k = 0; k < 12; ++k) {
+        const float4 v = __ldg(src + k);
+        sh.v[4 * k] = v.x; sh.v[4 * k + 1] = v.y; sh.v[4 * k + 2] = v.z; sh.v[4 * k + 3] = v.w;
+      }
+      sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
+    } else {
+      ShGlobal sh{a.shs + (size_t)idx * M * 3};
+      sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
+    }
+    g_mean[0] += gdir[0]; g_mean[1] += gdir[1]; g_mean[2] += gdir[2];
+    if (gp.shs) {
+      const int n = sh_num_coeffs(cam.sh_degree);
+      if (M == 16) {
+        float out[48];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float bk = (k < n) ? basis[k] : 0.f;
+          out[3 * k] = bk * grgb[0]; out[3 * k + 1] = bk * grgb[1]; out[3 * k + 2] = bk * grgb[2];
+        }
+        float4* dst = reinterpret_cast<float4*>(gp.shs + (size_t)idx * 48);
+#pragma unroll
+        for (int k = 0; k < 12; ++k) {
+          float4 v = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+          if (gp.accumulate) { const float4 o = dst[k]; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+          dst[k] = v;
+        }
+      } else {
+        float* dst = gp.shs + (size_t)idx * 3 * M;
+        for (int k = 0; k < M; ++k) {
+          const float bk = (k < n) ? basis[k] : 0.f;
+          for (int c = 0; c < 3; ++c) {
+            const float v = bk * grgb[c];
+            if (gp.accumulate) dst[3 * k + c] += v; else dst[3 * k + c] = v;
+          }
+        }
+      }
+    }
+  }
+  // covariance
+  if (a.cov3D_precomp) {
+    if (gp.cov3D_precomp) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        if (gp.accumulate) gp.cov3D_precomp[6 * idx + k] += g_cov[k]; else gp.cov3D_precomp[6 * idx + k] = g_cov[k];
+      }
+    }
+  } else {
+    float g_scale[3], g_rot[4];
+    cov3d_backward(sc, cam.scale_modifier, q, g_cov, g_scale, g_rot);
+    if (gp.scales) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (gp.accumulate) gp.scales[3 * idx + k] += g_scale[k]; else gp.scales[3 * idx + k] = g_scale[k];
+      }
+    }
+    if (gp.rotations) {
+      float4* dst = reinterpret_cast<float4*>(gp.rotations) + idx;
+      float4 v = make_float4(g_rot[0], g_rot[1], g_rot[2], g_rot[3]);
+      if (gp.accumulate) { const float4 o = *dst; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+      *dst = v;
+    }
+  }
+  if (gp.means3D) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      if (gp.accumulate) gp.means3D[3 * idx + k] += g_mean[k]; else gp.means3D[3 * idx + k] = g_mean[k];
+    }
+  }
+  if (gp.means2D) {
+    if (gp.accumulate) { gp.means2D[3 * idx] += in.g_mean2d_x; gp.means2D[3 * idx + 1] += in.g_mean2d_y; }
+    else { gp.means2D[3 * idx] = in.g_mean2d_x; gp.means2D[3 * idx + 1] = in.g_mean2d_y; gp.means2D[3 * idx + 2] = 0.f; }
+  }
+  if (gp.opacities) {
+    if (gp.accumulate) gp.opacities[idx] += g_op; else gp.opacities[idx] = g_op;
+  }
+}
+
+__global__ void mark_visible_kernel(const float* __restrict__ means3D, const float* __restrict__ viewmatrix, int64_t P,
+                                    uint8_t* __restrict__ present) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  float vm[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) vm[k] = __ldg(viewmatrix + k);
+  const float z = affine_row(vm, 2, __ldg(means3D + 3 * idx), __ldg(means3D + 3 * idx + 1), __ldg(means3D + 3 * idx + 2));
+  present[idx] = (z > NEAR_Z) ? 1 : 0;
+}
+
+}  // namespace
+
+cudaError_t launch_preprocess(const DeviceArgs& a, GeomView g, int32_t* radii, cudaStream_t s) {
+  if (a.P <= 0) return cudaSuccess;
+  const unsigned blocks = (unsigned)((a.P + PRE_THREADS - 1) / PRE_THREADS);
+  preprocess_kernel<<<blocks, PRE_THREADS, 0, s>>>(a, g, radii);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const int32_t* radii, const float* acc,
+                                       GradPtrs gp, cudaStream_t s) {
+  if (a.P <= 0) return cudaSuccess;
+  const unsigned blocks = (unsigned)((a.P + PRE_THREADS - 1) / PRE_THREADS);
+  preprocess_backward_kernel<<<blocks, PRE_THREADS, 0, s>>>(a, g, radii, acc, gp);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_mark_visible(const float* means3D, const float* viewmatrix, int64_t P, uint8_t* present,
+                                cudaStream_t s) {
+  if (P <= 0) return cudaSuccess;
+  const unsigned blocks = (unsigned)((P + 255) / 256);
+  mark_visible_kernel<<<blocks, 256, 0, s>>>(means3D, viewmatrix, P, present);
+  return cudaGetLastError();
+}
+
+}  // namespace pdgs
