@@ -105,6 +105,19 @@ const char* pdgs_version(void);
 int pdgs_create(PdgsHandle** out);
 int pdgs_destroy(PdgsHandle* h);
 
+/* Per-stage device timing (no reference counterpart; the reference times whole iterations with
+ * two CUDA events, /root/reference/train.py:87-88,121,186).  When enabled, forward/backward record
+ * CUDA events on the caller's stream between stages; pdgs_stage_times() waits for the last
+ * recorded event and returns the duration in ms of every stage of the most recent forward and
+ * backward on this handle (0 for a stage that did not run). */
+enum {
+  PDGS_STAGE_PREPROCESS = 0, PDGS_STAGE_SCAN = 1, PDGS_STAGE_DUPLICATE = 2, PDGS_STAGE_SORT = 3,
+  PDGS_STAGE_RANGES = 4, PDGS_STAGE_BLEND_FWD = 5, PDGS_STAGE_BWD_ZERO = 6, PDGS_STAGE_BLEND_BWD = 7,
+  PDGS_STAGE_PREPROCESS_BWD = 8, PDGS_STAGE_COUNT = 9
+};
+int pdgs_set_stage_timing(PdgsHandle* h, int32_t enable);
+int pdgs_stage_times(PdgsHandle* h, float* ms, int32_t n);
+
 size_t pdgs_geom_bytes(int64_t P);
 size_t pdgs_image_bytes(int32_t width, int32_t height);
 size_t pdgs_binning_bytes(int64_t capacity_pairs, int64_t P);

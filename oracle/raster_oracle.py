@@ -144,7 +144,7 @@ class Oracle:
 
     def __init__(self, settings: Settings, means3D, opacities, shs=None, colors_precomp=None, scales=None,
                  rotations=None, cov3D_precomp=None, need_grad: bool = True, structure: Optional[dict] = None,
-                 tile_window: Optional[tuple] = None):
+                 tile_window: Optional[tuple] = None, round_pixel_centre: bool = True):
         s = settings
         self.s = s
         self.W, self.H = int(s.image_width), int(s.image_height)
@@ -152,6 +152,8 @@ class Oracle:
         self.need_grad = need_grad
         self.structure = structure
         self.tile_window = tile_window  # (tx0, ty0, tx1, ty1) restrict blending to a tile window
+        # False only for finite-difference self-checks (the fp32 rounding of the pixel centre is a step function)
+        self.round_pixel_centre = round_pixel_centre
         self.means3D = _leaf64(means3D, need_grad)
         self.opacities = _leaf64(opacities, need_grad)
         self.shs = _leaf64(shs, need_grad)
@@ -227,6 +229,8 @@ class Oracle:
         radius = torch.ceil(3.0 * torch.sqrt(lam.detach())).to(torch.int64)
         pix = torch.stack([((ndc[:, 0] + 1.0) * W - 1.0) * 0.5, ((ndc[:, 1] + 1.0) * H - 1.0) * 0.5], dim=1)
         pix32 = pix.detach().to(torch.float32).to(torch.float64)  # reference rounds the pixel centre to fp32
+        if not self.round_pixel_centre:
+            pix32 = pix.detach()
         depth = p_view[:, 2]
         if self.structure is not None:  # integer side taken from the fp32 bit-model
             st = self.structure

@@ -19,6 +19,20 @@ struct PdgsHandle {
   int device;
   unsigned long long* host_slot;  // pinned: [0] = num_rendered | overflow << 32
   cudaEvent_t ev;
+  int timing;                                  // per-stage events enabled
+  cudaEvent_t t_begin[PDGS_STAGE_COUNT], t_end[PDGS_STAGE_COUNT];
+  bool t_valid[PDGS_STAGE_COUNT];
+};
+
+// Brackets one stage with events on the launching stream when timing is on.
+struct StageTimer {
+  PdgsHandle* h; int stage; cudaStream_t s;
+  StageTimer(PdgsHandle* h_, int stage_, cudaStream_t s_) : h(h_), stage(stage_), s(s_) {
+    if (h->timing) cudaEventRecord(h->t_begin[stage], s);
+  }
+  ~StageTimer() {
+    if (h->timing) { cudaEventRecord(h->t_end[stage], s); h->t_valid[stage] = true; }
+  }
 };
 
 static thread_local char g_err[512] = "";
@@ -58,6 +72,12 @@ int pdgs_create(PdgsHandle** out) {
   }
   PD_CUDA(cudaHostAlloc((void**)&h->host_slot, 64, cudaHostAllocDefault));
   PD_CUDA(cudaEventCreateWithFlags(&h->ev, cudaEventDisableTiming));
+  h->timing = 0;
+  for (int i = 0; i < PDGS_STAGE_COUNT; ++i) {
+    PD_CUDA(cudaEventCreate(&h->t_begin[i]));
+    PD_CUDA(cudaEventCreate(&h->t_end[i]));
+    h->t_valid[i] = false;
+  }
   *out = h;
   return PDGS_OK;
 }
@@ -66,7 +86,26 @@ int pdgs_destroy(PdgsHandle* h) {
   if (!h) return PDGS_OK;
   cudaFreeHost(h->host_slot);
   cudaEventDestroy(h->ev);
+  for (int i = 0; i < PDGS_STAGE_COUNT; ++i) { cudaEventDestroy(h->t_begin[i]); cudaEventDestroy(h->t_end[i]); }
   delete h;
+  return PDGS_OK;
+}
+
+int pdgs_set_stage_timing(PdgsHandle* h, int32_t enable) {
+  if (!h) return fail(PDGS_E_INVALID, "pdgs_set_stage_timing: handle is NULL");
+  h->timing = enable ? 1 : 0;
+  for (int i = 0; i < PDGS_STAGE_COUNT; ++i) h->t_valid[i] = false;
+  return PDGS_OK;
+}
+
+int pdgs_stage_times(PdgsHandle* h, float* ms, int32_t n) {
+  if (!h || !ms || n < PDGS_STAGE_COUNT) return fail(PDGS_E_INVALID, "pdgs_stage_times: bad argument");
+  for (int i = 0; i < PDGS_STAGE_COUNT; ++i) {
+    ms[i] = 0.f;
+    if (!h->t_valid[i]) continue;
+    PD_CUDA(cudaEventSynchronize(h->t_end[i]));
+    PD_CUDA(cudaEventElapsedTime(&ms[i], h->t_begin[i], h->t_end[i]));
+  }
   return PDGS_OK;
 }
 
@@ -126,19 +165,31 @@ static int make_args(const PdgsScene* sc, const PdgsCamera* cam, DeviceArgs& a) 
     }                                                                                                 \
   } while (0)
 
-static int run_binning_and_blend(const DeviceArgs& a, GeomView g, ImageView im, PdgsState* st, const int32_t* radii,
-                                 const PdgsForwardOut* out, int debug, cudaStream_t s) {
+static int run_binning_and_blend(PdgsHandle* h, const DeviceArgs& a, GeomView g, ImageView im, PdgsState* st,
+                                 const int32_t* radii, const PdgsForwardOut* out, int debug, cudaStream_t s) {
   BinningView b = carve_binning(st->binning, st->capacity_pairs);
   if (b.bytes > st->binning_bytes) return fail(PDGS_E_INVALID, "binning buffer smaller than pdgs_binning_bytes(capacity)");
   const int tiles = a.grid_x * a.grid_y;
   const int npass = num_sort_passes(tiles);
   uint64_t* kin = (npass % 2 == 0) ? b.keys_a : b.keys_b;
   uint32_t* vin = (npass % 2 == 0) ? b.point_list : b.vals_b;
-  PD_STEP(debug, s, launch_duplicate(a, g, radii, kin, vin, st->capacity_pairs, s));
-  PD_STEP(debug, s, launch_sort(b.keys_a, b.point_list, b.keys_b, b.vals_b, &g.ctrl->num_rendered, st->capacity_pairs,
-                                npass, b.sort_scratch, s));
-  PD_STEP(debug, s, launch_ranges(b.keys_a, &g.ctrl->num_rendered, st->capacity_pairs, im.ranges, tiles, s));
-  PD_STEP(debug, s, launch_render_forward(a, g, im, b.point_list, st->capacity_pairs, out->color, out->invdepth, s));
+  {
+    StageTimer t(h, PDGS_STAGE_DUPLICATE, s);
+    PD_STEP(debug, s, launch_duplicate(a, g, radii, kin, vin, st->capacity_pairs, s));
+  }
+  {
+    StageTimer t(h, PDGS_STAGE_SORT, s);
+    PD_STEP(debug, s, launch_sort(b.keys_a, b.point_list, b.keys_b, b.vals_b, &g.ctrl->num_rendered,
+                                  st->capacity_pairs, npass, b.sort_scratch, s));
+  }
+  {
+    StageTimer t(h, PDGS_STAGE_RANGES, s);
+    PD_STEP(debug, s, launch_ranges(b.keys_a, &g.ctrl->num_rendered, st->capacity_pairs, im.ranges, tiles, s));
+  }
+  {
+    StageTimer t(h, PDGS_STAGE_BLEND_FWD, s);
+    PD_STEP(debug, s, launch_render_forward(a, g, im, b.point_list, st->capacity_pairs, out->color, out->invdepth, s));
+  }
   return PDGS_OK;
 }
 
@@ -160,12 +211,18 @@ int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, P
   if (!resume) {
     PD_CUDA(cudaMemsetAsync(g.ctrl, 0, sizeof(Ctrl), s));
     PD_CUDA(cudaMemsetAsync(g.scan_state, 0, ((size_t)(a.P > 0 ? a.P : 1) + SCAN_TILE - 1) / SCAN_TILE * 8, s));
-    PD_STEP(debug, s, launch_preprocess(a, g, out->radii, s));
-    PD_STEP(debug, s, launch_scan(g, a.P, s));
+    {
+      StageTimer t(h, PDGS_STAGE_PREPROCESS, s);
+      PD_STEP(debug, s, launch_preprocess(a, g, out->radii, s));
+    }
+    {
+      StageTimer t(h, PDGS_STAGE_SCAN, s);
+      PD_STEP(debug, s, launch_scan(g, a.P, s));
+    }
     PD_CUDA(cudaMemcpyAsync(h->host_slot, g.ctrl, 8, cudaMemcpyDeviceToHost, s));
     PD_CUDA(cudaEventRecord(h->ev, s));
     if (have_binning) {
-      rc = run_binning_and_blend(a, g, im, state, out->radii, out, debug, s);
+      rc = run_binning_and_blend(h, a, g, im, state, out->radii, out, debug, s);
       if (rc != PDGS_OK) return rc;
     }
     PD_CUDA(cudaEventSynchronize(h->ev));
@@ -180,7 +237,7 @@ int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, P
   // resume: geometry state is valid, R known; (re)run binning + blend with a big-enough buffer
   if (!have_binning) return fail(PDGS_E_INVALID, "resume without a binning buffer");
   if (*num_rendered > state->capacity_pairs) return fail(PDGS_E_INVALID, "resume: capacity < num_rendered");
-  return run_binning_and_blend(a, g, im, state, out->radii, out, debug, s);
+  return run_binning_and_blend(h, a, g, im, state, out->radii, out, debug, s);
 }
 
 int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, const PdgsState* state,
@@ -200,17 +257,24 @@ int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, 
   ImageView im = carve_image(state->image, a.W, a.H);
   const int debug = cam->debug;
   float* acc = (float*)scratch;
-  PD_CUDA(cudaMemsetAsync(acc, 0, (size_t)a.P * ACC_FLOATS * sizeof(float), s));
+  {
+    StageTimer t(h, PDGS_STAGE_BWD_ZERO, s);
+    PD_CUDA(cudaMemsetAsync(acc, 0, (size_t)a.P * ACC_FLOATS * sizeof(float), s));
+  }
   if (num_rendered > 0) {
     if (!state->binning) return fail(PDGS_E_INVALID, "binning buffer is NULL");
     BinningView b = carve_binning(state->binning, state->capacity_pairs);
+    StageTimer t(h, PDGS_STAGE_BLEND_BWD, s);
     PD_STEP(debug, s, launch_render_backward(a, g, im, b.point_list, dL_dcolor, dL_dinvdepth, acc, s));
   }
   GradPtrs gp;
   gp.means3D = grads->means3D; gp.means2D = grads->means2D; gp.shs = grads->shs;
   gp.colors_precomp = grads->colors_precomp; gp.opacities = grads->opacities; gp.scales = grads->scales;
   gp.rotations = grads->rotations; gp.cov3D_precomp = grads->cov3D_precomp; gp.accumulate = grads->accumulate;
-  PD_STEP(debug, s, launch_preprocess_backward(a, g, radii, acc, gp, s));
+  {
+    StageTimer t(h, PDGS_STAGE_PREPROCESS_BWD, s);
+    PD_STEP(debug, s, launch_preprocess_backward(a, g, radii, acc, gp, s));
+  }
   return PDGS_OK;
 }
 

@@ -1,0 +1,309 @@
+"""Host side of the rasterizer above the C ABI: the role of the reference's rasterize_points.cu
+glue (`RasterizeGaussiansCUDA`, `RasterizeGaussiansBackwardCUDA`, `markVisible`; source absent
+from /root/reference, interface per SURVEY.md 8(a) rows a5/a6 and Appendix B, caller at
+/root/reference/gaussian_renderer/__init__.py:104-112).
+
+PyTorch is used for device memory and the current stream only; all arithmetic happens in
+libpdgs.so.  Argument order and return tuples of `rasterize_gaussians` /
+`rasterize_gaussians_backward` / `mark_visible` follow the reference module's `_C` entry points.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+
+# per-device speculative capacity of the binning buffer (pairs); follows the last pair count
+_capacity_hint = {}
+# number of kernels of ours launched by the last forward / backward (for bench.py's gpu_launches)
+LAUNCHES_FORWARD = 0
+LAUNCHES_BACKWARD = 0
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    if t is None or t.numel() == 0:
+        return None
+    return C.c_void_p(t.data_ptr())
+
+
+def _f32c(t: Optional[torch.Tensor], name: str, device) -> Optional[torch.Tensor]:
+    if t is None or t.numel() == 0:
+        return None
+    if not t.is_cuda:
+        raise L.PdgsError(f"{name} must be a CUDA tensor (this rasterizer has no CPU path)")
+    if t.device != device:
+        raise L.PdgsError(f"{name} is on {t.device}, expected {device}")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _passes(tiles: int) -> int:
+    bits = 0
+    while (1 << bits) <= tiles and bits < 31:
+        bits += 1
+    return (32 + bits + 7) // 8
+
+
+def _camera(bg, scale_modifier, viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh_degree, campos, prefiltered,
+            antialiasing, debug) -> L.PdgsCamera:
+    cam = L.PdgsCamera()
+    cam.image_height, cam.image_width = int(H), int(W)
+    cam.tanfovx, cam.tanfovy = float(tanfovx), float(tanfovy)
+    cam.bg = _ptr(bg)
+    cam.scale_modifier = float(scale_modifier)
+    cam.viewmatrix, cam.projmatrix = _ptr(viewmatrix), _ptr(projmatrix)
+    cam.sh_degree = int(sh_degree)
+    cam.campos = _ptr(campos)
+    cam.prefiltered, cam.debug, cam.antialiasing = int(bool(prefiltered)), int(bool(debug)), int(bool(antialiasing))
+    return cam
+
+
+def _scene(P, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp) -> L.PdgsScene:
+    sc = L.PdgsScene()
+    sc.P = int(P)
+    sc.M = int(sh.shape[1]) if sh is not None else 0
+    sc.means3D, sc.shs, sc.colors_precomp = _ptr(means3D), _ptr(sh), _ptr(colors_precomp)
+    sc.opacities, sc.scales, sc.rotations = _ptr(opacities), _ptr(scales), _ptr(rotations)
+    sc.cov3D_precomp = _ptr(cov3D_precomp)
+    return sc
+
+
+def _state(geom, image, binning, capacity) -> L.PdgsState:
+    st = L.PdgsState()
+    st.geom, st.geom_bytes = _ptr(geom), geom.numel()
+    st.image, st.image_bytes = _ptr(image), image.numel()
+    st.binning = _ptr(binning)
+    st.binning_bytes = 0 if binning is None else binning.numel()
+    st.capacity_pairs = int(capacity)
+    return st
+
+
+def _binning_capacity(binning: Optional[torch.Tensor]) -> int:
+    """The capacity a binning blob was allocated for is stored in its python attribute."""
+    return int(getattr(binning, "_pdgs_capacity", 0)) if binning is not None else 0
+
+
+def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, sh, sh_degree, campos,
+                        prefiltered, antialiasing, debug):
+    """-> (num_rendered, color[3,H,W], radii[P] int32, geomBuffer, binningBuffer, imgBuffer, invdepths[1,H,W])."""
+    global LAUNCHES_FORWARD
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise L.PdgsError("means3D must have dimensions (num_points, 3)")
+    lib = L.lib()
+    dev = means3D.device
+    if not means3D.is_cuda:
+        raise L.PdgsError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
+    P, H, W = means3D.shape[0], int(image_height), int(image_width)
+    means3D = _f32c(means3D, "means3D", dev)
+    sh = _f32c(sh, "sh", dev)
+    colors_precomp = _f32c(colors_precomp, "colors_precomp", dev)
+    opacities = _f32c(opacities, "opacities", dev)
+    scales = _f32c(scales, "scales", dev)
+    rotations = _f32c(rotations, "rotations", dev)
+    cov3D_precomp = _f32c(cov3D_precomp, "cov3D_precomp", dev)
+    bg = _f32c(bg, "bg", dev)
+    viewmatrix = _f32c(viewmatrix, "viewmatrix", dev)
+    projmatrix = _f32c(projmatrix, "projmatrix", dev)
+    campos = _f32c(campos, "campos", dev)
+    if sh is not None and sh.dim() != 3:
+        raise L.PdgsError("sh must have dimensions (num_points, num_coeffs, 3)")
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        u8 = dict(dtype=torch.uint8, device=dev)
+        color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+        invdepth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
+        radii = torch.empty(P, dtype=torch.int32, device=dev)
+        geom = torch.empty(lib.pdgs_geom_bytes(P), **u8)
+        image = torch.empty(lib.pdgs_image_bytes(W, H), **u8)
+        cap = int(_capacity_hint.get(dev, 0)) if P > 0 else 0
+        binning = None
+        if cap > 0:
+            binning = torch.empty(lib.pdgs_binning_bytes(cap, P), **u8)
+        cam = _camera(bg, scale_modifier, viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh_degree, campos,
+                      prefiltered, antialiasing, debug)
+        sc = _scene(P, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp)
+        st = _state(geom, image, binning, cap)
+        out = L.PdgsForwardOut(_ptr(color), _ptr(invdepth), _ptr(radii))
+        R = C.c_int64(0)
+        rc = L.check(lib.pdgs_forward(h, C.byref(sc), C.byref(cam), C.byref(st), C.byref(out), 0, C.byref(R), stream),
+                     "pdgs_forward")
+        tiles = ((W + 15) // 16) * ((H + 15) // 16)
+        launches = 2 if P > 0 else 0                       # preprocess, scan
+        per_bin = 1 + 1 + _passes(tiles) + 1 + 1           # duplicate, histogram, passes, ranges, blend
+        if cap > 0:
+            launches += per_bin
+        if rc == L.PDGS_NEED_BINNING:
+            cap = max(int(R.value * 1.25) + 4096, 4096)
+            binning = torch.empty(lib.pdgs_binning_bytes(cap, P), **u8)
+            st = _state(geom, image, binning, cap)
+            L.check(lib.pdgs_forward(h, C.byref(sc), C.byref(cam), C.byref(st), C.byref(out), 1, C.byref(R), stream),
+                    "pdgs_forward(resume)")
+            launches += per_bin
+        if P > 0:
+            _capacity_hint[dev] = max(int(R.value * 1.25) + 4096, 4096)
+        if binning is None:
+            binning = torch.empty(0, **u8)
+        binning._pdgs_capacity = cap
+        LAUNCHES_FORWARD = launches
+    return int(R.value), color, radii, geom, binning, image, invdepth
+
+
+def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, scales, rotations, scale_modifier,
+                                 cov3D_precomp, viewmatrix, projmatrix, tanfovx, tanfovy, grad_out_color,
+                                 grad_out_invdepth, sh, sh_degree, campos, geomBuffer, num_rendered, binningBuffer,
+                                 imgBuffer, antialiasing, debug, accumulate_into: Optional[dict] = None):
+    """-> (grad_means2D[P,3], grad_colors_precomp[P,3], grad_opacities[P,1], grad_means3D[P,3],
+           grad_cov3Ds_precomp[P,6], grad_sh[P,M,3], grad_scales[P,3], grad_rotations[P,4]).
+
+    accumulate_into (extension used by the view-parallel path): a dict of preallocated gradient
+    tensors keyed like PdgsGrads; the kernel adds into them instead of writing fresh tensors."""
+    global LAUNCHES_BACKWARD
+    lib = L.lib()
+    dev = means3D.device
+    P = means3D.shape[0]
+    H, W = int(grad_out_color.shape[-2]), int(grad_out_color.shape[-1])
+    means3D = _f32c(means3D, "means3D", dev)
+    sh = _f32c(sh, "sh", dev)
+    colors_precomp = _f32c(colors_precomp, "colors_precomp", dev)
+    opacities = _f32c(opacities, "opacities", dev)
+    scales = _f32c(scales, "scales", dev)
+    rotations = _f32c(rotations, "rotations", dev)
+    cov3D_precomp = _f32c(cov3D_precomp, "cov3D_precomp", dev)
+    bg = _f32c(bg, "bg", dev)
+    viewmatrix = _f32c(viewmatrix, "viewmatrix", dev)
+    projmatrix = _f32c(projmatrix, "projmatrix", dev)
+    campos = _f32c(campos, "campos", dev)
+    grad_out_color = _f32c(grad_out_color, "grad_out_color", dev)
+    grad_out_invdepth = _f32c(grad_out_invdepth, "grad_out_invdepth", dev)
+    M = sh.shape[1] if sh is not None else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        g = L.PdgsGrads()
+        if accumulate_into is None:
+            # the kernel writes every row (zeros for culled Gaussians), so no memset is needed
+            dmeans2D = torch.empty(P, 3, **f32)
+            dmeans3D = torch.empty(P, 3, **f32)
+            dopac = torch.empty(P, 1, **f32)
+            dcolors = torch.empty(P, 3, **f32) if colors_precomp is not None else torch.zeros(P, 3, **f32)
+            dsh = torch.empty(P, M, 3, **f32) if sh is not None else torch.zeros(P, 0, 3, **f32)
+            dcov = torch.empty(P, 6, **f32) if cov3D_precomp is not None else torch.zeros(P, 6, **f32)
+            dscales = torch.empty(P, 3, **f32) if scales is not None else torch.zeros(P, 3, **f32)
+            drots = torch.empty(P, 4, **f32) if rotations is not None else torch.zeros(P, 4, **f32)
+            g.accumulate = 0
+        else:
+            a = accumulate_into
+            dmeans2D, dmeans3D, dopac = a.get("means2D"), a.get("means3D"), a.get("opacities")
+            dcolors, dsh, dcov = a.get("colors_precomp"), a.get("shs"), a.get("cov3D_precomp")
+            dscales, drots = a.get("scales"), a.get("rotations")
+            g.accumulate = 1
+        g.means3D, g.means2D, g.shs = _ptr(dmeans3D), _ptr(dmeans2D), _ptr(dsh) if sh is not None else None
+        g.colors_precomp = _ptr(dcolors) if colors_precomp is not None else None
+        g.opacities = _ptr(dopac)
+        g.scales = _ptr(dscales) if scales is not None else None
+        g.rotations = _ptr(drots) if rotations is not None else None
+        g.cov3D_precomp = _ptr(dcov) if cov3D_precomp is not None else None
+        if P > 0:
+            scratch = torch.empty(lib.pdgs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
+            cam = _camera(bg, scale_modifier, viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh_degree, campos,
+                          False, antialiasing, debug)
+            sc = _scene(P, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp)
+            st = _state(geomBuffer, imgBuffer, binningBuffer, _binning_capacity(binningBuffer))
+            L.check(lib.pdgs_backward(h, C.byref(sc), C.byref(cam), C.byref(st), _ptr(radii), int(num_rendered),
+                                      _ptr(grad_out_color), _ptr(grad_out_invdepth), _ptr(scratch), scratch.numel(),
+                                      C.byref(g), stream), "pdgs_backward")
+            LAUNCHES_BACKWARD = 2 if num_rendered > 0 else 1
+    return dmeans2D, dcolors, dopac, dmeans3D, dcov, dsh, dscales, drots
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """-> bool[P]; the near-plane test of the reference's checkFrustum."""
+    lib = L.lib()
+    if not means3D.is_cuda:
+        raise L.PdgsError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
+    dev = means3D.device
+    P = means3D.shape[0]
+    means3D = _f32c(means3D, "means3D", dev)
+    viewmatrix = _f32c(viewmatrix, "viewmatrix", dev)
+    projmatrix = _f32c(projmatrix, "projmatrix", dev)
+    present = torch.zeros(P, dtype=torch.bool, device=dev)
+    if P > 0:
+        with torch.cuda.device(dev):
+            stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            L.check(lib.pdgs_mark_visible(_ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix), P, _ptr(present), stream),
+                    "pdgs_mark_visible")
+    return present
+
+
+def sort_pairs(keys: torch.Tensor, vals: torch.Tensor, end_bit: int):
+    """Stable radix sort of (uint64 key as int64 tensor, uint32 value as int32 tensor) pairs over
+    key bits [0, end_bit) with the rasterizer's onesweep kernels.  Inputs are clobbered."""
+    lib = L.lib()
+    dev = keys.device
+    n = keys.numel()
+    assert keys.dtype == torch.int64 and vals.dtype == torch.int32 and vals.numel() == n
+    keys_out, vals_out = torch.empty_like(keys), torch.empty_like(vals)
+    if n == 0:
+        return keys_out, vals_out
+    with torch.cuda.device(dev):
+        nb = lib.pdgs_sort_scratch_bytes(n)
+        scratch = torch.empty(nb, dtype=torch.uint8, device=dev)
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        L.check(lib.pdgs_sort_pairs(_ptr(keys), _ptr(vals), _ptr(keys_out), _ptr(vals_out), n, int(end_bit),
+                                    _ptr(scratch), nb, stream), "pdgs_sort_pairs")
+    return keys_out, vals_out
+
+
+def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int) -> dict:
+    """Copies of the saved state as torch tensors (parity tests)."""
+    lib = L.lib()
+    st = _state(geom, image, binning if binning.numel() else None, _binning_capacity(binning))
+    v = L.PdgsStateView()
+    L.check(lib.pdgs_state_view(C.byref(st), P, W, H, C.byref(v)), "pdgs_state_view")
+    dev = geom.device
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+
+    def grab(ptr, count, dtype):
+        if not ptr or count == 0:
+            return torch.empty(0, dtype=dtype)
+        nbytes = count * torch.empty(0, dtype=dtype).element_size()
+        # locate the view inside its blob and slice
+        for blob in (geom, binning, image):
+            if blob.numel() and blob.data_ptr() <= ptr < blob.data_ptr() + blob.numel():
+                off = ptr - blob.data_ptr()
+                return blob[off:off + nbytes].view(dtype).clone().cpu()
+        raise L.PdgsError("state view pointer outside the state blobs")
+
+    R = int(num_rendered)
+    return dict(
+        point_list=grab(v.point_list, R, torch.int32), sorted_keys=grab(v.sorted_keys, R, torch.int64),
+        ranges=grab(v.ranges, tiles * 2, torch.int32).view(-1, 2), final_T=grab(v.final_T, W * H, torch.float32),
+        n_contrib=grab(v.n_contrib, W * H, torch.int32), tiles_touched=grab(v.tiles_touched, P, torch.int32),
+        point_offsets=grab(v.point_offsets, P, torch.int32), xy=grab(v.xy, P * 4, torch.float32).view(-1, 4),
+        conic_opacity=grab(v.conic_opacity, P * 4, torch.float32).view(-1, 4),
+        rgb=grab(v.rgb, P * 4, torch.float32).view(-1, 4))
+
+
+def set_stage_timing(device, enable: bool) -> None:
+    """Turn the library's per-stage CUDA-event timing on/off for this thread's handle on `device`."""
+    dev = torch.device(device)
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        L.check(L.lib().pdgs_set_stage_timing(h, int(bool(enable))), "pdgs_set_stage_timing")
+
+
+def stage_times(device) -> dict:
+    """Durations (ms) of the stages of the most recent forward/backward on `device` (waits for them)."""
+    dev = torch.device(device)
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        buf = (C.c_float * len(L.STAGES))()
+        L.check(L.lib().pdgs_stage_times(h, buf, len(L.STAGES)), "pdgs_stage_times")
+    return {name: float(buf[i]) for i, name in enumerate(L.STAGES)}
