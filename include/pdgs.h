@@ -154,6 +154,8 @@ typedef struct PdgsStateView {
   const uint32_t* ranges;       /* [T,2] */
   const float* final_T;         /* [H*W] */
   const uint32_t* n_contrib;    /* [H*W] */
+  const uint32_t* n_tested;     /* [H*W] list entries evaluated by the forward blend */
+  const uint32_t* n_accepted;   /* [H*W] list entries blended */
   const uint32_t* tiles_touched;/* [P] */
   const uint32_t* point_offsets;/* [P] inclusive scan */
   const float* xy;              /* [P,4] (x, y, conic.x, conic.y) */

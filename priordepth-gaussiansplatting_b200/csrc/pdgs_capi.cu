@@ -322,6 +322,8 @@ int pdgs_state_view(const PdgsState* state, int64_t P, int32_t width, int32_t he
   view->ranges = (const uint32_t*)im.ranges;
   view->final_T = im.final_T;
   view->n_contrib = im.n_contrib;
+  view->n_tested = im.n_tested;
+  view->n_accepted = im.n_accepted;
   view->tiles_touched = g.tiles_touched;
   view->point_offsets = g.point_offsets;
   view->xy = (const float*)g.gA;

@@ -67,6 +67,8 @@ struct ImageView {
   uint2* ranges;        // [tiles]
   float* final_T;       // [H*W]
   uint32_t* n_contrib;  // [H*W]
+  uint32_t* n_tested;   // [H*W] list entries evaluated before the pixel stopped (roofline bookkeeping)
+  uint32_t* n_accepted; // [H*W] entries blended into the pixel
   size_t bytes;
 };
 
@@ -79,6 +81,8 @@ inline __host__ ImageView carve_image(void* base, int W, int H) {
   v.ranges = (uint2*)(p + off); off += align_up(tiles * sizeof(uint2));
   v.final_T = (float*)(p + off); off += align_up(hw * sizeof(float));
   v.n_contrib = (uint32_t*)(p + off); off += align_up(hw * sizeof(uint32_t));
+  v.n_tested = (uint32_t*)(p + off); off += align_up(hw * sizeof(uint32_t));
+  v.n_accepted = (uint32_t*)(p + off); off += align_up(hw * sizeof(uint32_t));
   v.bytes = off;
   return v;
 }

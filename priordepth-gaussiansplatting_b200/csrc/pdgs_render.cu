@@ -42,7 +42,9 @@ __global__ void __launch_bounds__(RT) render_forward_kernel(const float4* __rest
                                                             const uint32_t* __restrict__ point_list, int W, int H,
                                                             const float* __restrict__ bg, float* __restrict__ out_color,
                                                             float* __restrict__ out_invdepth, float* __restrict__ final_T,
-                                                            uint32_t* __restrict__ n_contrib) {
+                                                            uint32_t* __restrict__ n_contrib,
+                                                            uint32_t* __restrict__ n_tested,
+                                                            uint32_t* __restrict__ n_accepted) {
   __shared__ float4 sA[RT];  // x, y, -0.5*conA, -conB
   __shared__ float4 sB[RT];  // -0.5*conC, opacity, 1/depth, -
   __shared__ float4 sC[RT];  // r, g, b
@@ -53,7 +55,7 @@ __global__ void __launch_bounds__(RT) render_forward_kernel(const float4* __rest
   const float pxf = (float)px, pyf = (float)py;
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
-  uint32_t contributor = 0, last = 0;
+  uint32_t contributor = 0, last = 0, accepted = 0;
   bool done = !inside;
   for (uint32_t base = range.x; base < range.y; base += RT) {
     if (__syncthreads_count(done) == RT) break;
@@ -89,12 +91,15 @@ __global__ void __launch_bounds__(RT) render_forward_kernel(const float4* __rest
       D = fmaf(b.z, w, D);
       T = test_T;
       last = contributor;
+      ++accepted;
     }
   }
   if (inside) {
     const size_t pix = (size_t)py * W + px, hw = (size_t)W * H;
     final_T[pix] = T;
     n_contrib[pix] = last;
+    n_tested[pix] = contributor;
+    n_accepted[pix] = accepted;
     out_color[pix] = C0 + T * __ldg(bg + 0);
     out_color[hw + pix] = C1 + T * __ldg(bg + 1);
     out_color[2 * hw + pix] = C2 + T * __ldg(bg + 2);
@@ -232,7 +237,7 @@ cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im,
   if (a.W <= 0 || a.H <= 0) return cudaSuccess;
   dim3 grid(a.grid_x, a.grid_y);
   render_forward_kernel<<<grid, RT, 0, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, a.W, a.H, a.bg, out_color,
-                                            out_invdepth, im.final_T, im.n_contrib);
+                                            out_invdepth, im.final_T, im.n_contrib, im.n_tested, im.n_accepted);
   return cudaGetLastError();
 }
 

@@ -49,7 +49,7 @@ class PdgsGrads(C.Structure):
 
 
 class PdgsStateView(C.Structure):
-    _fields_ = [("point_list", vp), ("sorted_keys", vp), ("ranges", vp), ("final_T", vp), ("n_contrib", vp),
+    _fields_ = [("point_list", vp), ("sorted_keys", vp), ("ranges", vp), ("final_T", vp), ("n_contrib", vp), ("n_tested", vp), ("n_accepted", vp),
                 ("tiles_touched", vp), ("point_offsets", vp), ("xy", vp), ("conic_opacity", vp), ("rgb", vp)]
 
 

@@ -285,7 +285,8 @@ def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int) 
     return dict(
         point_list=grab(v.point_list, R, torch.int32), sorted_keys=grab(v.sorted_keys, R, torch.int64),
         ranges=grab(v.ranges, tiles * 2, torch.int32).view(-1, 2), final_T=grab(v.final_T, W * H, torch.float32),
-        n_contrib=grab(v.n_contrib, W * H, torch.int32), tiles_touched=grab(v.tiles_touched, P, torch.int32),
+        n_contrib=grab(v.n_contrib, W * H, torch.int32), n_tested=grab(v.n_tested, W * H, torch.int32),
+        n_accepted=grab(v.n_accepted, W * H, torch.int32), tiles_touched=grab(v.tiles_touched, P, torch.int32),
         point_offsets=grab(v.point_offsets, P, torch.int32), xy=grab(v.xy, P * 4, torch.float32).view(-1, 4),
         conic_opacity=grab(v.conic_opacity, P * 4, torch.float32).view(-1, 4),
         rgb=grab(v.rgb, P * 4, torch.float32).view(-1, 4))

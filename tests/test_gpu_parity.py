@@ -164,7 +164,8 @@ def test_edge_cases():
     view = sc.views[0]
     sc.bg = torch.tensor([0.25, 0.5, 0.75])
     # (a) everything behind the camera
-    sc_b = scenes.Scene(**{**sc.__dict__, "means3D": sc.means3D * torch.tensor([1.0, 1.0, -1.0]) - torch.tensor([0, 0, 1.0])})
+    behind = torch.stack([sc.means3D[:, 0], sc.means3D[:, 1], -sc.means3D[:, 2].abs() - 1.0], dim=1).contiguous()
+    sc_b = scenes.Scene(**{**sc.__dict__, "means3D": behind})
     lv, color, radii, invd = helpers.run_cuda(sc_b, view, DEV)
     assert int(radii.max()) == 0
     assert torch.allclose(color.cpu(), sc.bg[:, None, None].expand(3, 32, 48))
