@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""Benchmark of the rasterizer hot path on BASELINE.json's headline configuration.
+
+Workload (config 4): a batch of 64 cameras (1600x1064) around ~3M Gaussians (SH degree 3), fwd + image
+loss + bwd per view, views sharded contiguously over the ranks (one process per GPU), per-Gaussian
+gradients summed with one all-reduce per step.  One "step" = the whole 64-view batch.
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun, one rank per GPU)
+  python bench.py --impl reference ...                     CPU arm: the float64 oracle on the host cores
+
+Prints ONE JSON line (rank 0).  `value` = views/s with all inputs resident in HBM; `e2e` = the same
+batch step fed from pinned HOST buffers (Gaussians, cameras, target images copied host->device and
+the loss read back inside the timed region).  `roofline` describes the kernel that takes the largest
+share of the step, `stages` every stage; durations are CUDA-event pairs recorded on the launching
+stream inside the timed region (pdgs_set_stage_timing).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "priordepth-gaussiansplatting_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch  # noqa: E402
+
+METRIC = "fwd+bwd raster views/s @1.6K px, ~3M Gaussians (batch of 64 cameras, view-parallel)"
+UNIT = "views/s"
+SM_COUNT, FP32_LANES = 148, 128
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="C4")
+    ap.add_argument("--views", type=int, default=64)
+    ap.add_argument("--P", type=int, default=None, help="override the Gaussian count (debugging only)")
+    ap.add_argument("--scale-image", type=float, default=1.0, help="debugging only")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-window", type=int, nargs=2, default=[12, 8], help="tile window of the CPU sample")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm_gbs=float(d["hbm_gbs"]), sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)), source="measured")
+    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
+
+
+# --------------------------------------------------------------------------------------------
+# CPU arm: the float64 oracle on a bounded sample (tile window of one view), extrapolated by pairs
+# --------------------------------------------------------------------------------------------
+def oracle_sample(scene, view, window_tiles, threads):
+    """fwd+bwd of the oracle on the Gaussians touching a centred window of tiles of `view`.
+    Returns (seconds, pairs in the window, pairs in the whole view)."""
+    import numpy as np
+    from oracle import bitmodel
+    from oracle.raster_oracle import Oracle, Settings
+    torch.set_num_threads(threads)
+    W, H = view.image_width, view.image_height
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    tw, th = min(window_tiles[0], gx), min(window_tiles[1], gy)
+    x0, y0 = (gx - tw) // 2, (gy - th) // 2
+    win = (x0, y0, x0 + tw, y0 + th)
+    st = bitmodel.preprocess(scene.means3D, scene.scales, 1.0, scene.rotations, None, view.world_view_transform,
+                             view.full_proj_transform, W, H, np.float32(view.tanfovx), np.float32(view.tanfovy))
+    rect, vis = st["rect"], st["radii"] > 0
+    hit = vis & (rect[:, 0] < win[2]) & (rect[:, 2] > win[0]) & (rect[:, 1] < win[3]) & (rect[:, 3] > win[1])
+    ids = torch.from_numpy(np.nonzero(hit)[0])
+    cx0, cx1 = np.clip(rect[hit, 0], win[0], win[2]), np.clip(rect[hit, 2], win[0], win[2])
+    cy0, cy1 = np.clip(rect[hit, 1], win[1], win[3]), np.clip(rect[hit, 3], win[1], win[3])
+    pairs_window = int(((cx1 - cx0) * (cy1 - cy0)).sum())
+    pairs_view = int(st["num_rendered"])
+    sub = {k: (v[hit] if hasattr(v, "shape") and v.shape[:1] == hit.shape else v) for k, v in st.items()}
+    sub["num_rendered"] = int(sub["tiles"].sum())
+    s = Settings(image_height=H, image_width=W, tanfovx=view.tanfovx, tanfovy=view.tanfovy, bg=scene.bg,
+                 scale_modifier=1.0, viewmatrix=view.world_view_transform, projmatrix=view.full_proj_transform,
+                 sh_degree=scene.sh_degree, campos=view.camera_center)
+    gen = torch.Generator().manual_seed(7)
+    target = torch.rand(3, H, W, generator=gen, dtype=torch.float64)
+    t0 = time.perf_counter()
+    o = Oracle(s, scene.means3D[ids], scene.opacities[ids], shs=scene.shs[ids], scales=scene.scales[ids],
+               rotations=scene.rotations[ids], need_grad=True, structure=sub, tile_window=win)
+    res = o.forward()
+    gc = torch.sign(res.color - target) / target.numel()
+    o.backward(gc, None)
+    dt = time.perf_counter() - t0
+    return dt, pairs_window, pairs_view, int(ids.numel())
+
+
+def cpu_arm(args, scene, steps, warmup):
+    threads = os.cpu_count() or 1
+    view = scene.views[0]
+    times, info = [], None
+    for it in range(warmup + steps):
+        dt, pw, pv, n = oracle_sample(scene, view, args.cpu_window, threads)
+        info = (pw, pv, n)
+        if it >= warmup:
+            times.append(dt)
+    pw, pv, n = info
+    t_sample = sum(times) / len(times)
+    t_view = t_sample * pv / max(pw, 1)
+    sample = (f"float64 PyTorch-CPU oracle, fwd+bwd, {args.cpu_window[0]}x{args.cpu_window[1]}-tile centred window of "
+              f"view 0 ({n} Gaussians, {pw} of {pv} (tile,Gaussian) pairs); {t_sample:.2f} s per sample, "
+              f"extrapolated to a whole view by pairs")
+    return dict(value=1.0 / t_view, unit=UNIT, cores=threads, kind="port", sample=sample), t_sample
+
+
+# --------------------------------------------------------------------------------------------
+def start_clock_sampler(gpu_index):
+    f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+    q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    try:
+        proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                 "-lms", "100"], stdout=f, stderr=subprocess.DEVNULL)
+    except OSError:
+        return None, f.name
+    return proc, f.name
+
+
+def stop_clock_sampler(proc, path):
+    out = dict(sm_mhz=None, sm_max_mhz=None, reasons=[], samples=0)
+    if proc is not None:
+        proc.terminate()
+        try:
+            proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            proc.kill()
+    try:
+        rows = [r.strip().split(",") for r in open(path) if r.strip()]
+        os.unlink(path)
+    except OSError:
+        rows = []
+    sm, reasons = [], set()
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    for r in rows:
+        if len(r) < 7:
+            continue
+        try:
+            sm.append(float(r[0]))
+            out["sm_max_mhz"] = float(r[1])
+        except ValueError:
+            continue
+        for k, name in enumerate(names):
+            if r[3 + k].strip().lower() == "active":
+                reasons.add(name)
+    if sm:
+        sm.sort()
+        out["sm_mhz"] = sm[len(sm) // 2]
+        out["samples"] = len(sm)
+    out["reasons"] = sorted(reasons)
+    return out
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    from pdgs_b200 import scenes
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        scene = scenes.make_config(args.config, P=args.P, n_views=args.views, scale_image=args.scale_image)
+        t0 = time.perf_counter()
+        base, t_sample = cpu_arm(args, scene, max(1, args.steps), max(0, min(args.warmup, 1)))
+        line = dict(impl="reference", metric=METRIC, value=base["value"], unit=UNIT, n_gpus=args.gpus, steps=args.steps,
+                    warmup=args.warmup, ms_per_step=1e3 * args.views / base["value"], higher_is_better=True,
+                    scaling="strong", vs_baseline=None, dtype="f64", data="synthetic",
+                    config=workload_config(args, scene, world=1), cpu_baseline=base,
+                    e2e=dict(value=base["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                    gpu_launches=0, wall_s=time.perf_counter() - t0,
+                    note="the reference rasterizer is CUDA-only and its source is absent from the checkout; this arm is "
+                         "the float64 CPU transcription of its maths (oracle/) on the host cores")
+        print(json.dumps(line))
+        return 0
+
+    assert torch.cuda.is_available(), "bench.py needs a B200: the rasterizer has no CPU path"
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from diff_gaussian_rasterization import GaussianRasterizationSettings
+    from pdgs_b200 import rasterizer as rz
+    from pdgs_b200.viewparallel import ViewParallelRasterizer, shard_views
+
+    scene = scenes.make_config(args.config, P=args.P, n_views=args.views, scale_image=args.scale_image)
+    P, M = scene.P, scene.shs.shape[1]
+    host = dict(means3D=scene.means3D, shs=scene.shs, opacities=scene.opacities, scales=scene.scales,
+                rotations=scene.rotations)
+    host = {k: v.contiguous().pin_memory() for k, v in host.items()}
+    g_dev = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+    my = shard_views(len(scene.views), rank, world)
+    H, W = scene.views[0].image_height, scene.views[0].image_width
+
+    def settings(view, mats):
+        return GaussianRasterizationSettings(
+            image_height=view.image_height, image_width=view.image_width, tanfovx=view.tanfovx, tanfovy=view.tanfovy,
+            bg=mats["bg"], scale_modifier=1.0, viewmatrix=mats["view"], projmatrix=mats["proj"],
+            sh_degree=scene.sh_degree, campos=mats["campos"], prefiltered=False, debug=False, antialiasing=False)
+
+    # host-side per-view inputs (pinned): camera block [view 16 | proj 16 | campos 3 | bg 3] and the target image
+    cam_host, tgt_host = {}, {}
+    for i in my:
+        v = scene.views[i]
+        cam_host[i] = torch.cat([v.world_view_transform.reshape(-1), v.full_proj_transform.reshape(-1),
+                                 v.camera_center.reshape(-1), scene.bg.reshape(-1)]).float().pin_memory()
+        gen = torch.Generator().manual_seed(scenes.SEED0 + 1000 + i)
+        tgt_host[i] = torch.rand(3, H, W, generator=gen).pin_memory()
+
+    def cam_views(block):
+        return dict(view=block[0:16].view(4, 4), proj=block[16:32].view(4, 4), campos=block[32:35], bg=block[35:38])
+
+    cam_dev = {i: cam_host[i].to(dev) for i in my}
+    tgt_dev = {i: tgt_host[i].to(dev) for i in my}
+    views_dev = [settings(scene.views[i], cam_views(cam_dev[i])) if i in cam_dev else None for i in range(len(scene.views))]
+    vp = ViewParallelRasterizer(P, M, dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---------------- resident-input throughput (`value`) ----------------
+    for _ in range(args.warmup):
+        vp.step(g_dev, views_dev, tgt_dev)
+    barrier()
+    rz.set_stage_timing(dev, True)
+    sampler, sampler_path = start_clock_sampler(local_rank) if rank == 0 else (None, None)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches, pairs = 0, []
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        vp.step(g_dev, views_dev, tgt_dev)
+        launches += vp.last_launches
+        pairs.extend(vp.last_num_rendered)
+    e1.record()
+    barrier()
+    clocks = stop_clock_sampler(sampler, sampler_path) if rank == 0 else None
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    stage = rz.stage_times(dev)
+    rz.set_stage_timing(dev, False)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        lt = torch.tensor([launches], dtype=torch.int64, device=dev)
+        dist.all_reduce(lt)
+        launches = int(lt.item())
+    ms_total = float(ms.item())
+    n_views = len(scene.views)
+    value = n_views * args.steps / (ms_total * 1e-3)
+    loss_mean = float(vp.loss_acc[0].item()) / n_views
+
+    # ---------------- algorithmic work of this rank's views (untimed pass) ----------------
+    work = dict(P=P, V=0, R=0, n_test=0, n_acc=0, n_test_bwd=0, views=len(my), tiles=((W + 15) // 16) * ((H + 15) // 16),
+                HW=H * W)
+    empty = torch.empty(0, device=dev)
+    with torch.no_grad():
+        for i in my:
+            rs = views_dev[i]
+            R, color, radii, geom, binning, img, invd = rz.rasterize_gaussians(
+                rs.bg, g_dev["means3D"], empty, g_dev["opacities"], g_dev["scales"], g_dev["rotations"], 1.0, empty,
+                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, H, W, g_dev["shs"], rs.sh_degree, rs.campos, False,
+                False, False)
+            c = rz.image_counters(geom, binning, img, P, W, H)
+            work["V"] += int((radii > 0).sum().item())
+            work["R"] += int(R)
+            work["n_test"] += c["n_tested"]
+            work["n_acc"] += c["n_accepted"]
+            work["n_test_bwd"] += c["n_contrib"]
+    torch.cuda.synchronize(dev)
+
+    # ---------------- end-to-end with host buffers (`e2e`) ----------------
+    e2e = None
+    if not args.no_e2e:
+        h2d = sum(v.numel() * 4 for v in host.values()) + sum(cam_host[i].numel() * 4 + tgt_host[i].numel() * 4 for i in my)
+        d2h = 8
+
+        def e2e_step():
+            g = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+            vs = [None] * n_views
+            tg = {}
+            for i in my:
+                vs[i] = settings(scene.views[i], cam_views(cam_host[i].to(dev, non_blocking=True)))
+                tg[i] = tgt_host[i].to(dev, non_blocking=True)
+            out = vp.step(g, vs, tg)
+            return out["loss_sums"].cpu()  # device -> host read of the step's result (synchronises)
+
+        for _ in range(max(1, min(args.warmup, 2))):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(args.steps):
+            last = e2e_step()
+        e1.record()
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([max(wall, e0.elapsed_time(e1))], dtype=torch.float64, device=dev)
+        hb = torch.tensor([h2d, d2h], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(hb)
+        e2e = dict(value=n_views * args.steps / (float(t.item()) * 1e-3), unit=UNIT, h2d_bytes_per_step=int(hb[0].item()),
+                   d2h_bytes_per_step=int(hb[1].item()), ms_per_step=float(t.item()) / args.steps,
+                   api="pdgs_b200.viewparallel.ViewParallelRasterizer.step (C ABI: pdgs_forward / pdgs_image_loss / "
+                       "pdgs_backward) fed from pinned host tensors",
+                   loss_mean=float(last[0].item()) / n_views)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---------------- roofline per stage (rank 0's launches) ----------------
+    peaks = measured_peaks()
+    fp32_peak = SM_COUNT * FP32_LANES * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s at the max SM clock
+    nv = max(work["views"], 1)
+    Pn, V, R = work["P"], work["V"] / nv, work["R"] / nv
+    T, HW = work["tiles"], work["HW"]
+    npass = (32 + max(1, T.bit_length()) + 7) // 8
+    alg = {  # algorithmic bytes / flops per launch (= per view), SURVEY.md 8(d)
+        "preprocess": ("hbm", 12 * Pn + 224 * V + 8 * Pn + 40 * V),
+        "scan": ("hbm", 8 * Pn),
+        "duplicate": ("hbm", 4 * Pn + 16 * V + 12 * R),
+        "sort": ("hbm", 8 * R + npass * 24 * R),
+        "ranges": ("hbm", 8 * R + 8 * T),
+        "blend_fwd": ("fp32_simt", 15 * work["n_test"] / nv + 11 * work["n_acc"] / nv),
+        "bwd_zero": ("hbm", 48 * Pn),
+        "blend_bwd": ("fp32_simt", 15 * work["n_test_bwd"] / nv + 59 * work["n_acc"] / nv),
+        "preprocess_bwd": ("hbm", 284 * V + 236 * Pn),
+        "loss": ("hbm", 36 * HW),
+    }
+    traffic = {}
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath))
+    stages, total_stage_ms = [], sum(v[0] for v in stage.values())
+    for name, (ms_sum, cnt) in stage.items():
+        if cnt == 0:
+            continue
+        bound, amount = alg[name]
+        avg_ms = ms_sum / cnt
+        if bound == "hbm":
+            achieved, peak, unit = amount / (avg_ms * 1e-3) / 1e9, peaks["hbm_gbs"], "GB/s"
+        else:
+            achieved, peak, unit = amount / (avg_ms * 1e-3) / 1e12, fp32_peak, "TFLOP/s"
+        stages.append(dict(stage=name, bound=bound, avg_ms=avg_ms, launches=cnt, share=ms_sum / max(total_stage_ms, 1e-9),
+                           achieved=achieved, peak=peak, unit=unit, frac=achieved / peak,
+                           traffic=traffic.get(name)))
+    stages.sort(key=lambda s: -s["share"])
+    top = stages[0] if stages else None
+    roofline = None
+    if top:
+        roofline = dict(kernel=top["stage"], bound=top["bound"], achieved=top["achieved"], peak=top["peak"], unit=top["unit"],
+                        frac=top["frac"], traffic=top["traffic"], avg_ms=top["avg_ms"], share_of_step=top["share"],
+                        peak_source=("MEASURED_PEAKS.json hbm_gbs (%s)" % peaks["source"]) if top["bound"] == "hbm" else
+                        "derived: 148 SMs x 128 fp32 lanes x 2 x sm_max_mhz (MEASURED_PEAKS.json has no fp32 SIMT figure)")
+
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu_baseline, _ = cpu_arm(args, scene, 1, 0)
+
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
+                ms_per_step=ms_total / args.steps, ms_per_view_per_gpu=ms_total / args.steps / max(len(my), 1),
+                higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
+                config=workload_config(args, scene, world), clocks=clocks, e2e=e2e, gpu_launches=launches,
+                roofline=roofline, stages=stages, cpu_baseline=cpu_baseline,
+                work_per_view=dict(P=Pn, visible=V, pairs=R, n_test=work["n_test"] / nv, n_acc=work["n_acc"] / nv,
+                                   n_test_bwd=work["n_test_bwd"] / nv),
+                loss_mean=loss_mean)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def workload_config(args, scene, world):
+    v = scene.views[0]
+    return dict(workload=f"{args.config}: {scene.P} Gaussians SH3, {len(scene.views)} cameras {v.image_width}x{v.image_height}, "
+                         f"fwd + L1 loss + bwd per view, grads summed over views",
+                gaussians=scene.P, views_per_step=len(scene.views), image=[v.image_width, v.image_height],
+                parallelism=f"view-parallel x{world} (Gaussians replicated, one all-reduce of [P,61] fp32 per step)",
+                l2_policy="inputs larger than L2 (708 MB of Gaussian parameters streamed per view vs 126 MB L2); no flush")
+
+
+if __name__ == "__main__":
+    sys.exit(main())

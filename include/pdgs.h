@@ -97,6 +97,12 @@ typedef struct PdgsGrads {       /* any pointer may be NULL = not wanted */
   float* rotations;      /* [P,4] */
   float* cov3D_precomp;  /* [P,6] */
   int32_t accumulate;    /* 0: overwrite (dense, zeros for culled); 1: += into the buffers */
+  /* Optional densification statistics of this view, updated for visible Gaussians (radii > 0) in the
+   * same pass; they replace the caller-side torch ops at /root/reference/scene/gaussian_model.py:502-506
+   * and /root/reference/train.py:313-314.  NULL = not wanted. */
+  float* densify_grad_accum; /* [P] += || dL/dmeans2D.xy ||  (xyz_gradient_accum) */
+  float* densify_denom;      /* [P] += 1                      (denom) */
+  int32_t* max_radii2D;      /* [P]  = max(old, radii)        (max_radii2D) */
 } PdgsGrads;
 
 const char* pdgs_last_error(void);
@@ -106,17 +112,17 @@ int pdgs_create(PdgsHandle** out);
 int pdgs_destroy(PdgsHandle* h);
 
 /* Per-stage device timing (no reference counterpart; the reference times whole iterations with
- * two CUDA events, /root/reference/train.py:87-88,121,186).  When enabled, forward/backward record
- * CUDA events on the caller's stream between stages; pdgs_stage_times() waits for the last
- * recorded event and returns the duration in ms of every stage of the most recent forward and
- * backward on this handle (0 for a stage that did not run). */
+ * two CUDA events, /root/reference/train.py:87-88,121,186).  When enabled, every stage of every
+ * forward/backward/loss call on this handle is bracketed by a CUDA event pair on the caller's
+ * stream (no host synchronisation).  pdgs_stage_times() waits for the recorded pairs, returns per
+ * stage the SUM of durations in ms and the number of pairs since the previous call, and resets. */
 enum {
   PDGS_STAGE_PREPROCESS = 0, PDGS_STAGE_SCAN = 1, PDGS_STAGE_DUPLICATE = 2, PDGS_STAGE_SORT = 3,
   PDGS_STAGE_RANGES = 4, PDGS_STAGE_BLEND_FWD = 5, PDGS_STAGE_BWD_ZERO = 6, PDGS_STAGE_BLEND_BWD = 7,
-  PDGS_STAGE_PREPROCESS_BWD = 8, PDGS_STAGE_COUNT = 9
+  PDGS_STAGE_PREPROCESS_BWD = 8, PDGS_STAGE_LOSS = 9, PDGS_STAGE_COUNT = 10
 };
 int pdgs_set_stage_timing(PdgsHandle* h, int32_t enable);
-int pdgs_stage_times(PdgsHandle* h, float* ms, int32_t n);
+int pdgs_stage_times(PdgsHandle* h, float* ms_sum, int32_t* counts, int32_t n);
 
 size_t pdgs_geom_bytes(int64_t P);
 size_t pdgs_image_bytes(int32_t width, int32_t height);
@@ -136,6 +142,17 @@ int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, P
 int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, const PdgsState* state,
                   const int32_t* radii, int64_t num_rendered, const float* dL_dcolor, const float* dL_dinvdepth,
                   void* scratch, size_t scratch_bytes, const PdgsGrads* grads, void* stream);
+
+/* Image-space loss of one view and its cotangents in one pass (the caller-side torch ops at
+ * /root/reference/train.py:153 `l1_loss` = utils/loss_utils.py:40-41 and :174 the depth-prior term):
+ *   loss[0] += mean |color - target|                     over 3*H*W
+ *   loss[1] += mean |(invdepth - prior) * mask|          over H*W      (skipped when prior is NULL)
+ *   dL_dcolor    = w_color * sign(color - target) / (3*H*W)
+ *   dL_dinvdepth = w_depth * sign((invdepth - prior) * mask) * mask / (H*W)
+ * mask may be NULL (= ones).  loss is a 2-float DEVICE accumulator the caller zeroes. */
+int pdgs_image_loss(PdgsHandle* h, const float* color, const float* target, const float* invdepth,
+                    const float* prior, const float* mask, int32_t width, int32_t height, float w_color,
+                    float w_depth, float* dL_dcolor, float* dL_dinvdepth, float* loss, void* stream);
 
 int pdgs_mark_visible(const float* means3D, const float* viewmatrix, const float* projmatrix, int64_t P,
                       uint8_t* present, void* stream);

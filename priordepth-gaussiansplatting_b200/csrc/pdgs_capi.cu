@@ -10,28 +10,41 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <vector>
+
 #include "../../include/pdgs.h"
 #include "pdgs_internal.cuh"
 
 using namespace pdgs;
 
+struct StageRec { int stage; cudaEvent_t b, e; };
+
 struct PdgsHandle {
   int device;
   unsigned long long* host_slot;  // pinned: [0] = num_rendered | overflow << 32
   cudaEvent_t ev;
-  int timing;                                  // per-stage events enabled
-  cudaEvent_t t_begin[PDGS_STAGE_COUNT], t_end[PDGS_STAGE_COUNT];
-  bool t_valid[PDGS_STAGE_COUNT];
+  int timing;                     // per-stage events enabled
+  std::vector<cudaEvent_t> pool;  // idle timing events
+  std::vector<StageRec> recs;     // recorded since the last pdgs_stage_times()
 };
 
-// Brackets one stage with events on the launching stream when timing is on.
+static cudaEvent_t take_event(PdgsHandle* h) {
+  if (!h->pool.empty()) { cudaEvent_t e = h->pool.back(); h->pool.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+
+// Brackets one stage with a fresh event pair on the launching stream when timing is on; the pairs are
+// resolved (and recycled) only in pdgs_stage_times(), so timing adds no host synchronisation.
 struct StageTimer {
-  PdgsHandle* h; int stage; cudaStream_t s;
-  StageTimer(PdgsHandle* h_, int stage_, cudaStream_t s_) : h(h_), stage(stage_), s(s_) {
-    if (h->timing) cudaEventRecord(h->t_begin[stage], s);
+  PdgsHandle* h; cudaStream_t s; StageRec r;
+  StageTimer(PdgsHandle* h_, int stage_, cudaStream_t s_) : h(h_), s(s_) {
+    r.stage = stage_; r.b = r.e = nullptr;
+    if (h->timing) { r.b = take_event(h); r.e = take_event(h); cudaEventRecord(r.b, s); }
   }
   ~StageTimer() {
-    if (h->timing) { cudaEventRecord(h->t_end[stage], s); h->t_valid[stage] = true; }
+    if (r.b) { cudaEventRecord(r.e, s); h->recs.push_back(r); }
   }
 };
 
@@ -73,11 +86,6 @@ int pdgs_create(PdgsHandle** out) {
   PD_CUDA(cudaHostAlloc((void**)&h->host_slot, 64, cudaHostAllocDefault));
   PD_CUDA(cudaEventCreateWithFlags(&h->ev, cudaEventDisableTiming));
   h->timing = 0;
-  for (int i = 0; i < PDGS_STAGE_COUNT; ++i) {
-    PD_CUDA(cudaEventCreate(&h->t_begin[i]));
-    PD_CUDA(cudaEventCreate(&h->t_end[i]));
-    h->t_valid[i] = false;
-  }
   *out = h;
   return PDGS_OK;
 }
@@ -86,7 +94,8 @@ int pdgs_destroy(PdgsHandle* h) {
   if (!h) return PDGS_OK;
   cudaFreeHost(h->host_slot);
   cudaEventDestroy(h->ev);
-  for (int i = 0; i < PDGS_STAGE_COUNT; ++i) { cudaEventDestroy(h->t_begin[i]); cudaEventDestroy(h->t_end[i]); }
+  for (StageRec& r : h->recs) { cudaEventDestroy(r.b); cudaEventDestroy(r.e); }
+  for (cudaEvent_t e : h->pool) cudaEventDestroy(e);
   delete h;
   return PDGS_OK;
 }
@@ -94,18 +103,23 @@ int pdgs_destroy(PdgsHandle* h) {
 int pdgs_set_stage_timing(PdgsHandle* h, int32_t enable) {
   if (!h) return fail(PDGS_E_INVALID, "pdgs_set_stage_timing: handle is NULL");
   h->timing = enable ? 1 : 0;
-  for (int i = 0; i < PDGS_STAGE_COUNT; ++i) h->t_valid[i] = false;
+  for (StageRec& r : h->recs) { h->pool.push_back(r.b); h->pool.push_back(r.e); }
+  h->recs.clear();
   return PDGS_OK;
 }
 
-int pdgs_stage_times(PdgsHandle* h, float* ms, int32_t n) {
+int pdgs_stage_times(PdgsHandle* h, float* ms, int32_t* counts, int32_t n) {
   if (!h || !ms || n < PDGS_STAGE_COUNT) return fail(PDGS_E_INVALID, "pdgs_stage_times: bad argument");
-  for (int i = 0; i < PDGS_STAGE_COUNT; ++i) {
-    ms[i] = 0.f;
-    if (!h->t_valid[i]) continue;
-    PD_CUDA(cudaEventSynchronize(h->t_end[i]));
-    PD_CUDA(cudaEventElapsedTime(&ms[i], h->t_begin[i], h->t_end[i]));
+  for (int i = 0; i < PDGS_STAGE_COUNT; ++i) { ms[i] = 0.f; if (counts) counts[i] = 0; }
+  for (StageRec& r : h->recs) {
+    float t = 0.f;
+    PD_CUDA(cudaEventSynchronize(r.e));
+    PD_CUDA(cudaEventElapsedTime(&t, r.b, r.e));
+    ms[r.stage] += t;
+    if (counts) counts[r.stage] += 1;
+    h->pool.push_back(r.b); h->pool.push_back(r.e);
   }
+  h->recs.clear();
   return PDGS_OK;
 }
 
@@ -271,10 +285,25 @@ int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, 
   gp.means3D = grads->means3D; gp.means2D = grads->means2D; gp.shs = grads->shs;
   gp.colors_precomp = grads->colors_precomp; gp.opacities = grads->opacities; gp.scales = grads->scales;
   gp.rotations = grads->rotations; gp.cov3D_precomp = grads->cov3D_precomp; gp.accumulate = grads->accumulate;
+  gp.densify_grad_accum = grads->densify_grad_accum; gp.densify_denom = grads->densify_denom;
+  gp.max_radii2D = grads->max_radii2D;
   {
     StageTimer t(h, PDGS_STAGE_PREPROCESS_BWD, s);
     PD_STEP(debug, s, launch_preprocess_backward(a, g, radii, acc, gp, s));
   }
+  return PDGS_OK;
+}
+
+int pdgs_image_loss(PdgsHandle* h, const float* color, const float* target, const float* invdepth,
+                    const float* prior, const float* mask, int32_t width, int32_t height, float w_color,
+                    float w_depth, float* dL_dcolor, float* dL_dinvdepth, float* loss, void* stream) {
+  if (!h || !color || !target || !dL_dcolor || !loss || width <= 0 || height <= 0)
+    return fail(PDGS_E_INVALID, "pdgs_image_loss: bad argument");
+  if (prior && (!invdepth || !dL_dinvdepth)) return fail(PDGS_E_INVALID, "pdgs_image_loss: prior given without invdepth / dL_dinvdepth");
+  cudaStream_t s = (cudaStream_t)stream;
+  StageTimer t(h, PDGS_STAGE_LOSS, s);
+  PD_CUDA(launch_image_loss(color, target, invdepth, prior, mask, width, height, w_color, w_depth, dL_dcolor,
+                            dL_dinvdepth, loss, s));
   return PDGS_OK;
 }
 

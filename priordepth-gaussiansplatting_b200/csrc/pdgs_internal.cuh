@@ -170,9 +170,13 @@ cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im
 struct GradPtrs {
   float* means3D; float* means2D; float* shs; float* colors_precomp; float* opacities; float* scales;
   float* rotations; float* cov3D_precomp; int accumulate;
+  float* densify_grad_accum; float* densify_denom; int32_t* max_radii2D;
 };
 cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const int32_t* radii, const float* acc,
                                        GradPtrs gp, cudaStream_t s);
+cudaError_t launch_image_loss(const float* color, const float* target, const float* invdepth, const float* prior,
+                              const float* mask, int W, int H, float w_color, float w_depth, float* dL_dcolor,
+                              float* dL_dinvdepth, float* loss, cudaStream_t s);
 cudaError_t launch_mark_visible(const float* means3D, const float* viewmatrix, int64_t P, uint8_t* present,
                                 cudaStream_t s);
 

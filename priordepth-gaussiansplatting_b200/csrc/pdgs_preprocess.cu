@@ -242,6 +242,11 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
   if (gp.opacities) {
     if (gp.accumulate) gp.opacities[idx] += g_op; else gp.opacities[idx] = g_op;
   }
+  // densification statistics of this view (scene/gaussian_model.py:502-506, train.py:313-314)
+  if (gp.densify_grad_accum)
+    gp.densify_grad_accum[idx] += sqrtf(in.g_mean2d_x * in.g_mean2d_x + in.g_mean2d_y * in.g_mean2d_y);
+  if (gp.densify_denom) gp.densify_denom[idx] += 1.0f;
+  if (gp.max_radii2D) gp.max_radii2D[idx] = max(gp.max_radii2D[idx], radii[idx]);
 }
 
 __global__ void mark_visible_kernel(const float* __restrict__ means3D, const float* __restrict__ viewmatrix, int64_t P,

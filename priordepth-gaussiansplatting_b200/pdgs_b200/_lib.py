@@ -45,7 +45,8 @@ class PdgsForwardOut(C.Structure):
 
 class PdgsGrads(C.Structure):
     _fields_ = [("means3D", vp), ("means2D", vp), ("shs", vp), ("colors_precomp", vp), ("opacities", vp),
-                ("scales", vp), ("rotations", vp), ("cov3D_precomp", vp), ("accumulate", C.c_int32)]
+                ("scales", vp), ("rotations", vp), ("cov3D_precomp", vp), ("accumulate", C.c_int32),
+                ("densify_grad_accum", vp), ("densify_denom", vp), ("max_radii2D", vp)]
 
 
 class PdgsStateView(C.Structure):
@@ -60,7 +61,8 @@ SYMBOLS = {
     "pdgs_create": (C.c_int, [C.POINTER(vp)]),
     "pdgs_destroy": (C.c_int, [vp]),
     "pdgs_set_stage_timing": (C.c_int, [vp, C.c_int32]),
-    "pdgs_stage_times": (C.c_int, [vp, C.POINTER(C.c_float), C.c_int32]),
+    "pdgs_stage_times": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_int32]),
+    "pdgs_image_loss": (C.c_int, [vp, vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_float, C.c_float, vp, vp, vp, vp]),
     "pdgs_geom_bytes": (C.c_size_t, [C.c_int64]),
     "pdgs_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "pdgs_binning_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
@@ -75,7 +77,7 @@ SYMBOLS = {
     "pdgs_state_view": (C.c_int, [C.POINTER(PdgsState), C.c_int64, C.c_int32, C.c_int32, C.POINTER(PdgsStateView)]),
 }
 
-STAGES = ("preprocess", "scan", "duplicate", "sort", "ranges", "blend_fwd", "bwd_zero", "blend_bwd", "preprocess_bwd")
+STAGES = ("preprocess", "scan", "duplicate", "sort", "ranges", "blend_fwd", "bwd_zero", "blend_bwd", "preprocess_bwd", "loss")
 
 _lib = None
 _lock = threading.Lock()

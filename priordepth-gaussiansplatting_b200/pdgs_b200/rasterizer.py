@@ -21,6 +21,7 @@ _capacity_hint = {}
 # number of kernels of ours launched by the last forward / backward (for bench.py's gpu_launches)
 LAUNCHES_FORWARD = 0
 LAUNCHES_BACKWARD = 0
+LAUNCHES_LOSS = 0
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -210,6 +211,10 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
         g.scales = _ptr(dscales) if scales is not None else None
         g.rotations = _ptr(drots) if rotations is not None else None
         g.cov3D_precomp = _ptr(dcov) if cov3D_precomp is not None else None
+        if accumulate_into is not None:
+            g.densify_grad_accum = _ptr(accumulate_into.get("densify_grad_accum"))
+            g.densify_denom = _ptr(accumulate_into.get("densify_denom"))
+            g.max_radii2D = _ptr(accumulate_into.get("max_radii2D"))
         if P > 0:
             scratch = torch.empty(lib.pdgs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
             cam = _camera(bg, scale_modifier, viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh_degree, campos,
@@ -221,6 +226,35 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
                                       C.byref(g), stream), "pdgs_backward")
             LAUNCHES_BACKWARD = 2 if num_rendered > 0 else 1
     return dmeans2D, dcolors, dopac, dmeans3D, dcov, dsh, dscales, drots
+
+
+def image_loss(color, target, invdepth=None, prior=None, mask=None, w_color=1.0, w_depth=0.0, loss_acc=None):
+    """One-pass image loss + cotangents (C ABI pdgs_image_loss; the torch ops at
+    /root/reference/train.py:153,174).  -> (dL_dcolor[3,H,W], dL_dinvdepth[1,H,W] or None, loss_acc[2]);
+    loss_acc (device float[2]: mean L1, mean masked depth L1) is accumulated into when given."""
+    global LAUNCHES_LOSS
+    lib = L.lib()
+    dev = color.device
+    if not color.is_cuda:
+        raise L.PdgsError("color must be a CUDA tensor (this rasterizer has no CPU path)")
+    H, W = int(color.shape[-2]), int(color.shape[-1])
+    color = _f32c(color, "color", dev)
+    target = _f32c(target, "target", dev)
+    if target is None or target.numel() != color.numel():
+        raise L.PdgsError("target must have the shape of color")
+    invdepth, prior, mask = _f32c(invdepth, "invdepth", dev), _f32c(prior, "prior", dev), _f32c(mask, "mask", dev)
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        dcolor = torch.empty_like(color)
+        ddepth = torch.empty(1, H, W, dtype=torch.float32, device=dev) if prior is not None else None
+        if loss_acc is None:
+            loss_acc = torch.zeros(2, dtype=torch.float32, device=dev)
+        L.check(lib.pdgs_image_loss(h, _ptr(color), _ptr(target), _ptr(invdepth), _ptr(prior), _ptr(mask), W, H,
+                                    float(w_color), float(w_depth), _ptr(dcolor), _ptr(ddepth), _ptr(loss_acc), stream),
+                "pdgs_image_loss")
+        LAUNCHES_LOSS = 1
+    return dcolor, ddepth, loss_acc
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):
@@ -292,6 +326,20 @@ def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int) 
         rgb=grab(v.rgb, P * 4, torch.float32).view(-1, 4))
 
 
+def image_counters(geom, binning, image, P: int, W: int, H: int) -> dict:
+    """Sums over pixels of the forward blend's per-pixel counters, reduced on the device:
+    n_tested (list entries evaluated), n_accepted (entries blended), n_contrib (last contributing position)."""
+    lib = L.lib()
+    st = _state(geom, image, binning if binning.numel() else None, _binning_capacity(binning))
+    v = L.PdgsStateView()
+    L.check(lib.pdgs_state_view(C.byref(st), P, W, H, C.byref(v)), "pdgs_state_view")
+    out = {}
+    for name in ("n_tested", "n_accepted", "n_contrib"):
+        off = getattr(v, name) - image.data_ptr()
+        out[name] = int(image[off:off + 4 * W * H].view(torch.int32).sum(dtype=torch.int64).item())
+    return out
+
+
 def set_stage_timing(device, enable: bool) -> None:
     """Turn the library's per-stage CUDA-event timing on/off for this thread's handle on `device`."""
     dev = torch.device(device)
@@ -301,10 +349,12 @@ def set_stage_timing(device, enable: bool) -> None:
 
 
 def stage_times(device) -> dict:
-    """Durations (ms) of the stages of the most recent forward/backward on `device` (waits for them)."""
+    """{stage: (summed duration in ms, number of launches of the stage)} since the previous call on `device`
+    (waits for the recorded work)."""
     dev = torch.device(device)
     with torch.cuda.device(dev):
         h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
         buf = (C.c_float * len(L.STAGES))()
-        L.check(L.lib().pdgs_stage_times(h, buf, len(L.STAGES)), "pdgs_stage_times")
-    return {name: float(buf[i]) for i, name in enumerate(L.STAGES)}
+        cnt = (C.c_int32 * len(L.STAGES))()
+        L.check(L.lib().pdgs_stage_times(h, buf, cnt, len(L.STAGES)), "pdgs_stage_times")
+    return {name: (float(buf[i]), int(cnt[i])) for i, name in enumerate(L.STAGES)}

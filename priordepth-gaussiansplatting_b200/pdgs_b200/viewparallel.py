@@ -1,0 +1,149 @@
+"""View-parallel batch step over the rasterizer.
+
+The reference renders one camera per optimiser step (/root/reference/train.py:129-143, 184) and keeps
+the densification statistics with torch ops on the caller side (scene/gaussian_model.py:502-506,
+train.py:313-314).  BASELINE.json config 4 instead renders a BATCH of cameras: the views are sharded
+contiguously over the ranks (one process per GPU), the Gaussians are replicated, every rank
+accumulates the gradients of its views IN PLACE inside the preprocess-backward kernel
+(PdgsGrads.accumulate = 1) into one flat fp32 buffer, and a single all-reduce (NCCL over NVLink on the
+GPUs, gloo in the CPU tests) sums that buffer over ranks.  The result equals what repeated
+`loss.backward()` calls without `zero_grad` produce on one GPU.
+
+The rasterizer backend is libpdgs.so through `pdgs_b200.rasterizer`; there is no CPU path.  The
+backend argument exists so the host logic (sharding, buffer layout, collectives) can be exercised on
+CPU tensors with `gloo` by the tests, which inject their own per-view gradient function.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+# segments of the flat gradient buffer: (name, floats per Gaussian); shs uses M*3
+_SEGMENTS = (("means3D", 3), ("shs", None), ("opacities", 1), ("scales", 3), ("rotations", 4),
+             ("densify_grad_accum", 1), ("densify_denom", 1))
+
+
+def shard_views(n_views: int, rank: int, world: int) -> range:
+    """Contiguous split: rank r renders views [r*B/n, (r+1)*B/n); remainders go to the low ranks."""
+    base, rem = divmod(int(n_views), int(world))
+    lo = rank * base + min(rank, rem)
+    return range(lo, lo + base + (1 if rank < rem else 0))
+
+
+class GradBuffer:
+    """One flat fp32 buffer holding every per-Gaussian gradient plus the densification statistics
+    (61 floats per Gaussian for SH degree 3), each segment starting on a 16-byte boundary so the kernels'
+    float4 accesses stay aligned, and an int32 max_radii2D vector (reduced with MAX)."""
+
+    def __init__(self, P: int, M: int, device):
+        self.P, self.M = int(P), int(M)
+        off = 0
+        self._spans: Dict[str, tuple] = {}
+        for name, width in _SEGMENTS:
+            w = 3 * self.M if width is None else width
+            self._spans[name] = (off, self.P * w, w)
+            off += (self.P * w + 3) // 4 * 4
+        self.flat = torch.zeros(max(off, 4), dtype=torch.float32, device=device)
+        self.max_radii2D = torch.zeros(self.P, dtype=torch.int32, device=device)
+
+    def view(self, name: str) -> torch.Tensor:
+        off, n, w = self._spans[name]
+        t = self.flat[off:off + n]
+        if name == "shs":
+            return t.view(self.P, self.M, 3)
+        return t.view(self.P, w) if w > 1 or name == "opacities" else t.view(self.P)
+
+    def zero_(self) -> "GradBuffer":
+        self.flat.zero_()
+        self.max_radii2D.zero_()
+        return self
+
+    def accumulate_dict(self) -> Dict[str, torch.Tensor]:
+        d = {name: self.view(name) for name, _ in _SEGMENTS}
+        d["max_radii2D"] = self.max_radii2D
+        return d
+
+    def all_reduce(self, group=None) -> None:
+        """The only data-path collective of the view-parallel step."""
+        dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=group)
+
+    @property
+    def floats_per_gaussian(self) -> int:
+        return sum((3 * self.M if w is None else w) for _, w in _SEGMENTS)
+
+
+def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, mask, w_depth, acc: Dict, loss_acc):
+    """forward -> image loss -> backward (accumulating) of ONE view on the CUDA library."""
+    from . import rasterizer as rz
+    empty = torch.empty(0, device=gaussians["means3D"].device)
+    shs = gaussians.get("shs")
+    colors = gaussians.get("colors_precomp")
+    num_rendered, color, radii, geom, binning, img, invd = rz.rasterize_gaussians(
+        rs.bg, gaussians["means3D"], empty if colors is None else colors, gaussians["opacities"], gaussians["scales"],
+        gaussians["rotations"], rs.scale_modifier, empty, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+        rs.image_height, rs.image_width, empty if shs is None else shs, rs.sh_degree, rs.campos, False, rs.antialiasing,
+        rs.debug)
+    launches = rz.LAUNCHES_FORWARD
+    use_depth = prior is not None and w_depth != 0.0
+    dcolor, ddepth, _ = rz.image_loss(color, target, invd if use_depth else None, prior if use_depth else None,
+                                      mask if use_depth else None, 1.0, w_depth, loss_acc)
+    launches += rz.LAUNCHES_LOSS
+    rz.rasterize_gaussians_backward(
+        rs.bg, gaussians["means3D"], radii, empty if colors is None else colors, gaussians["opacities"],
+        gaussians["scales"], gaussians["rotations"], rs.scale_modifier, empty, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+        rs.tanfovy, dcolor, ddepth, empty if shs is None else shs, rs.sh_degree, rs.campos, geom, num_rendered, binning,
+        img, rs.antialiasing, rs.debug, accumulate_into=acc)
+    launches += rz.LAUNCHES_BACKWARD
+    return dict(num_rendered=num_rendered, launches=launches, radii=radii, color=color, invdepth=invd)
+
+
+class ViewParallelRasterizer:
+    """step(): fwd + loss + bwd of this rank's shard of a batch of views, then one all-reduce."""
+
+    def __init__(self, P: int, M: int, device, group=None, backend: Optional[Callable] = None):
+        self.device = torch.device(device)
+        self.group = group
+        self.backend = backend or _cuda_view_backend
+        if backend is None and self.device.type != "cuda":
+            raise RuntimeError("ViewParallelRasterizer: the rasterizer needs a CUDA device (there is no CPU path)")
+        self.buf = GradBuffer(P, M, self.device)
+        self.loss_acc = torch.zeros(2, dtype=torch.float32, device=self.device)
+        self.last_launches = 0
+        self.last_num_rendered: List[int] = []
+
+    @property
+    def world(self) -> int:
+        return dist.get_world_size(self.group) if dist.is_available() and dist.is_initialized() else 1
+
+    @property
+    def rank(self) -> int:
+        return dist.get_rank(self.group) if dist.is_available() and dist.is_initialized() else 0
+
+    def step(self, gaussians: Dict[str, torch.Tensor], views: Sequence, targets: Dict[int, torch.Tensor],
+             priors: Optional[Dict[int, torch.Tensor]] = None, masks: Optional[Dict[int, torch.Tensor]] = None,
+             w_depth: float = 0.0, reduce: bool = True, keep_outputs: bool = False) -> Dict:
+        """gaussians: means3D/shs/opacities/scales/rotations (post-activation, as render() passes them,
+        /root/reference/gaussian_renderer/__init__.py:57-112); views: one GaussianRasterizationSettings per
+        camera of the WHOLE batch (identical on every rank); targets/priors/masks: dict view index -> tensor
+        for at least this rank's shard.  Returns summed-over-views gradients (all ranks) in self.buf."""
+        my = shard_views(len(views), self.rank, self.world)
+        self.buf.zero_()
+        self.loss_acc.zero_()
+        acc = self.buf.accumulate_dict()
+        self.last_launches = 0
+        self.last_num_rendered = []
+        outs = []
+        for i in my:
+            r = self.backend(gaussians, views[i], targets[i], None if priors is None else priors.get(i),
+                             None if masks is None else masks.get(i), w_depth, acc, self.loss_acc)
+            self.last_launches += int(r.get("launches", 0))
+            self.last_num_rendered.append(int(r.get("num_rendered", 0)))
+            if keep_outputs:
+                outs.append(r)
+        if reduce and self.world > 1:
+            self.buf.all_reduce(self.group)
+            dist.all_reduce(self.loss_acc, op=dist.ReduceOp.SUM, group=self.group)
+        return dict(loss_sums=self.loss_acc, grads=self.buf, local_views=list(my), outputs=outs)

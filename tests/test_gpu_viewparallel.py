@@ -1,0 +1,89 @@
+"""GPU tests of the batch (view-parallel) entry point and the fused image loss, through the C ABI."""
+import pytest
+import torch
+
+import helpers
+from pdgs_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.mark.parametrize("W,H,depth", [(64, 48, False), (203, 117, True), (1, 1, True)])
+def test_image_loss_matches_torch(W, H, depth):
+    from pdgs_b200 import rasterizer as rz
+    gen = torch.Generator().manual_seed(W * 7 + H)
+    color = torch.rand(3, H, W, generator=gen).to(DEV).requires_grad_(True)
+    target = torch.rand(3, H, W, generator=gen).to(DEV)
+    target[0, 0, 0] = color[0, 0, 0].detach()  # sign(0) = 0
+    invd = torch.rand(1, H, W, generator=gen).to(DEV).requires_grad_(True)
+    prior = torch.rand(1, H, W, generator=gen).to(DEV)
+    mask = (torch.rand(1, H, W, generator=gen) > 0.4).float().to(DEV)
+    w = 0.37
+    l1 = (color - target).abs().mean()
+    ld = ((invd - prior) * mask).abs().mean()
+    (l1 + w * ld).backward() if depth else l1.backward()
+    dc, dd, acc = rz.image_loss(color.detach(), target, invd.detach() if depth else None, prior if depth else None,
+                                mask if depth else None, 1.0, w)
+    assert torch.allclose(dc, color.grad, rtol=0, atol=1e-12)
+    assert abs(float(acc[0]) - float(l1)) <= 1e-6
+    if depth:
+        assert torch.allclose(dd, invd.grad, rtol=1e-6, atol=1e-12)
+        assert abs(float(acc[1]) - float(ld)) <= 1e-6
+    else:
+        assert dd is None and float(acc[1]) == 0.0
+
+
+def test_batch_step_equals_sum_of_single_view_autograd():
+    """Gradients accumulated in-kernel over a batch == sum of per-view autograd gradients; densification
+    statistics == the reference's torch ops (scene/gaussian_model.py:502-506, train.py:313-314)."""
+    from pdgs_b200.viewparallel import ViewParallelRasterizer
+    sc = scenes.make_config("C4", P=8000, n_views=4, scale_image=0.12)
+    H, W = sc.views[0].image_height, sc.views[0].image_width
+    gen = torch.Generator().manual_seed(3)
+    targets = {i: torch.rand(3, H, W, generator=gen).to(DEV) for i in range(4)}
+    priors = {i: torch.rand(1, H, W, generator=gen).to(DEV) for i in range(4)}
+    masks = {i: (torch.rand(1, H, W, generator=gen) > 0.5).float().to(DEV) for i in range(4)}
+    w_depth = 0.8
+    # reference: four autograd passes
+    sums, accum, denom, maxr, loss = None, torch.zeros(sc.P, device=DEV), torch.zeros(sc.P, device=DEV), \
+        torch.zeros(sc.P, dtype=torch.int32, device=DEV), 0.0
+    for i, view in enumerate(sc.views):
+        lv, color, radii, invd = helpers.run_cuda(sc, view, DEV)
+        l = (color - targets[i]).abs().mean() + w_depth * ((invd - priors[i]) * masks[i]).abs().mean()
+        l.backward()
+        loss += float((color - targets[i]).abs().mean())
+        g = {k: lv[k].grad for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        sums = g if sums is None else {k: sums[k] + g[k] for k in g}
+        vis = radii > 0
+        accum[vis] += lv["means2D"].grad[vis, :2].norm(dim=-1)
+        denom[vis] += 1
+        maxr[vis] = torch.max(maxr[vis], radii[vis])
+    vp = ViewParallelRasterizer(sc.P, 16, DEV)
+    gaussians = {k: getattr(sc, k).to(DEV) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    views = [helpers.cuda_settings(sc, v, DEV) for v in sc.views]
+    out = vp.step(gaussians, views, targets, priors, masks, w_depth)
+    assert out["local_views"] == [0, 1, 2, 3] and vp.last_launches > 0
+    for k in sums:
+        assert helpers.rel_err(vp.buf.view(k), sums[k].view_as(vp.buf.view(k))) < 2e-5, k
+    assert helpers.rel_err(vp.buf.view("densify_grad_accum"), accum) < 2e-5
+    assert torch.equal(vp.buf.view("densify_denom"), denom)
+    assert torch.equal(vp.buf.max_radii2D, maxr)
+    assert abs(float(vp.loss_acc[0]) - loss) < 1e-5
+    # a second step starts from zero again
+    vp.step(gaussians, views, targets, priors, masks, w_depth)
+    assert helpers.rel_err(vp.buf.view("shs"), sums["shs"]) < 2e-5
+
+
+def test_stage_timing_accumulates_without_sync():
+    from pdgs_b200 import rasterizer as rz
+    sc = scenes.camera_relative_scene("t", 8, 5000, 160, 120, 3.0)
+    rz.set_stage_timing(DEV, True)
+    for _ in range(3):
+        lv, color, radii, invd = helpers.run_cuda(sc, sc.views[0], DEV)
+        color.sum().backward()
+    st = rz.stage_times(DEV)
+    rz.set_stage_timing(DEV, False)
+    assert st["preprocess"][1] == 3 and st["blend_bwd"][1] == 3 and st["sort"][1] >= 3
+    assert all(ms >= 0.0 for ms, _ in st.values()) and st["blend_fwd"][0] > 0.0
+    assert rz.stage_times(DEV)["preprocess"][1] == 0
