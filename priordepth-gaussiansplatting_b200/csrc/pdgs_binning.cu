@@ -148,7 +148,7 @@ constexpr uint32_t LB_INC = 2u << 30;
 constexpr uint32_t LB_MASK = (1u << 30) - 1;
 
 __global__ void __launch_bounds__(256) sort_histogram_kernel(const uint64_t* __restrict__ keys, const uint32_t* n_dev,
-                                                             int64_t capacity, int npass, uint32_t* __restrict__ hist) {
+                                                             int64_t capacity, int npass, int end_bit, uint32_t* __restrict__ hist) {
   __shared__ uint32_t s_hist[MAX_PASSES * RADIX];
   const int64_t n = (int64_t)ld_volatile_u32(n_dev);
   if (n > capacity) return;
@@ -157,7 +157,10 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const uint64_t* __r
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const uint64_t k = keys[i];
-    for (int p = 0; p < npass; ++p) atomicAdd(&s_hist[p * RADIX + (int)((k >> (p * RADIX_BITS)) & (RADIX - 1))], 1u);
+    for (int p = 0; p < npass; ++p) {
+      const int nb = min(RADIX_BITS, end_bit - p * RADIX_BITS);  // the last pass may cover fewer than 8 bits
+      atomicAdd(&s_hist[p * RADIX + (int)((k >> (p * RADIX_BITS)) & ((1u << nb) - 1u))], 1u);
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < npass * RADIX; i += blockDim.x) {
@@ -170,7 +173,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     uint64_t* __restrict__ keys_out,
                                                                     uint32_t* __restrict__ vals_out, const uint32_t* n_dev,
-                                                                    int64_t capacity, int pass,
+                                                                    int64_t capacity, int pass, uint32_t digit_mask,
                                                                     const uint32_t* __restrict__ hist, uint32_t* ticket,
                                                                     uint32_t* lookback) {
   __shared__ uint64_t s_keys[SORT_TILE];
@@ -205,14 +208,14 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
       key[i] = keys_in[tile_base + local];
       val[i] = vals_in[tile_base + local];
     } else {
-      key[i] = ~0ull;  // sorts last in every pass (digit 255), excluded from the counts below
+      key[i] = ~0ull;  // padding: forced into the last bin below, excluded from the counts
       val[i] = 0u;
     }
   }
   // per-warp stable ranking with match_any
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; ++i) {
-    const uint32_t d = (uint32_t)(key[i] >> shift) & (RADIX - 1);
+    const uint32_t d = (seg + i * 32 + lane < valid) ? ((uint32_t)(key[i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
     const unsigned peers = __match_any_sync(0xffffffffu, d);
     const int leader = __ffs(peers) - 1;
     const uint32_t below = __popc(peers & ((1u << lane) - 1u));
@@ -279,7 +282,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
   // scatter into shared memory in sorted order
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; ++i) {
-    const uint32_t dd = (uint32_t)(key[i] >> shift) & (RADIX - 1);
+    const uint32_t dd = (seg + i * 32 + lane < valid) ? ((uint32_t)(key[i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
     const uint32_t slot = s_cta_base[dd] + s_wcnt[warp][dd] + rank[i];
     s_keys[slot] = key[i];
     s_vals[slot] = val[i];
@@ -288,7 +291,7 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
   // coalesced write-out; padding keys occupy slots >= valid and are dropped
   for (int j = threadIdx.x; j < valid; j += SORT_THREADS) {
     const uint64_t k = s_keys[j];
-    const uint32_t dd = (uint32_t)(k >> shift) & (RADIX - 1);
+    const uint32_t dd = (uint32_t)(k >> shift) & digit_mask;
     const uint32_t dst = s_goff[dd] + (uint32_t)j;
     keys_out[dst] = k;
     vals_out[dst] = s_vals[j];
@@ -335,7 +338,7 @@ cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, const int32_t* rad
 }
 
 cudaError_t launch_sort(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, const uint32_t* n_dev,
-                        int64_t capacity, int npass, void* scratch, cudaStream_t s) {
+                        int64_t capacity, int npass, int end_bit, void* scratch, cudaStream_t s) {
   if (capacity <= 0 || npass <= 0) return cudaSuccess;
   if (npass > MAX_PASSES) return cudaErrorInvalidValue;
   SortScratch sc = carve_sort_scratch(scratch, capacity);
@@ -348,12 +351,13 @@ cudaError_t launch_sort(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, ui
   int hist_blocks = (int)((capacity + 256 * 16 - 1) / (256 * 16));
   if (hist_blocks > 148 * 8) hist_blocks = 148 * 8;
   if (hist_blocks < 1) hist_blocks = 1;
-  sort_histogram_kernel<<<hist_blocks, 256, 0, s>>>(kin, n_dev, capacity, npass, sc.hist);
+  sort_histogram_kernel<<<hist_blocks, 256, 0, s>>>(kin, n_dev, capacity, npass, end_bit, sc.hist);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const unsigned tiles = (unsigned)sc.ntiles;
   for (int p = 0; p < npass; ++p) {
-    sort_onesweep_kernel<<<tiles, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, n_dev, capacity, p, sc.hist,
+    const int nb = (end_bit - p * RADIX_BITS < RADIX_BITS) ? end_bit - p * RADIX_BITS : RADIX_BITS;
+    sort_onesweep_kernel<<<tiles, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, n_dev, capacity, p, (1u << nb) - 1u, sc.hist,
                                                          sc.tickets + p, sc.lookback + (size_t)p * sc.ntiles * RADIX);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;

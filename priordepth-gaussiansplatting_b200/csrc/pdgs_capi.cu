@@ -194,7 +194,7 @@ static int run_binning_and_blend(PdgsHandle* h, const DeviceArgs& a, GeomView g,
   {
     StageTimer t(h, PDGS_STAGE_SORT, s);
     PD_STEP(debug, s, launch_sort(b.keys_a, b.point_list, b.keys_b, b.vals_b, &g.ctrl->num_rendered,
-                                  st->capacity_pairs, npass, b.sort_scratch, s));
+                                  st->capacity_pairs, npass, npass * RADIX_BITS, b.sort_scratch, s));
   }
   {
     StageTimer t(h, PDGS_STAGE_RANGES, s);
@@ -334,7 +334,7 @@ int pdgs_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, ui
     PD_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, s));
     PD_CUDA(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
   }
-  PD_CUDA(launch_sort(keys_out, vals_out, keys_in, vals_in, cnt, n, npass, scratch, s));
+  PD_CUDA(launch_sort(keys_out, vals_out, keys_in, vals_in, cnt, n, npass, end_bit, scratch, s));
   return PDGS_OK;
 }
 

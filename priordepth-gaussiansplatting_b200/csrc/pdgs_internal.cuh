@@ -158,9 +158,10 @@ cudaError_t launch_scan(GeomView g, int64_t P, cudaStream_t s);
 cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, const int32_t* radii, uint64_t* keys, uint32_t* vals,
                              int64_t capacity, cudaStream_t s);
 // Sorts pairs (keys_a, vals_a) <-> (keys_b, vals_b); input must sit in A if npass is even, in B if odd;
-// the result always lands in A.  n is read from *n_dev and must be <= capacity.
+// the result always lands in A.  n is read from *n_dev and must be <= capacity.  Key bits [0, end_bit) are
+// significant (npass = ceil(end_bit / 8); the last pass masks its digit to the remaining bits).
 cudaError_t launch_sort(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, const uint32_t* n_dev,
-                        int64_t capacity, int npass, void* scratch, cudaStream_t s);
+                        int64_t capacity, int npass, int end_bit, void* scratch, cudaStream_t s);
 cudaError_t launch_ranges(const uint64_t* keys, const uint32_t* n_dev, int64_t capacity, uint2* ranges, int tiles,
                           cudaStream_t s);
 cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,

@@ -124,12 +124,20 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
   const float4 a0 = __ldg(reinterpret_cast<const float4*>(acc) + 3 * idx);
   const float4 a1 = __ldg(reinterpret_cast<const float4*>(acc) + 3 * idx + 1);
   const float4 a2 = __ldg(reinterpret_cast<const float4*>(acc) + 3 * idx + 2);
-  const float4 gC = g.gC[idx];
+  const float4 gA = g.gA[idx], gB = g.gB[idx], gC = g.gC[idx];
   BwdIn in;
-  in.g_mean2d_x = a0.x; in.g_mean2d_y = a0.y;
-  in.g_conic_x = a0.z; in.g_conic_y = a0.w; in.g_conic_w = a1.x;
-  in.g_opacity = a1.y; in.g_invdepth = a1.z;
-  in.g_rgb[0] = a2.x; in.g_rgb[1] = a2.y; in.g_rgb[2] = a2.z;
+  {
+    // acc holds the raw pixel moments of z = G*dL/dalpha about the Gaussian's centre (pdgs_render.cu):
+    //   a0 = (sum z dx, sum z dy, sum z dx^2, sum z dx dy), a1 = (sum z dy^2, sum z, sum w dL/dD, -), a2 = sum w dL/dC
+    // with d = centre - pixel.  dL/dG = o*dL/dalpha, dG/dd = -G (A dx + B dy, C dy + B dx), dG/dconic = -0.5 G d d^T.
+    const float cA = gA.z, cB = gA.w, cC = gB.x, o = gB.y;
+    in.g_mean2d_x = -o * (0.5f * (float)a.W) * (cA * a0.x + cB * a0.y);
+    in.g_mean2d_y = -o * (0.5f * (float)a.H) * (cC * a0.y + cB * a0.x);
+    const float ho = -0.5f * o;
+    in.g_conic_x = ho * a0.z; in.g_conic_y = ho * a0.w; in.g_conic_w = ho * a1.x;
+    in.g_opacity = a1.y; in.g_invdepth = a1.z;
+    in.g_rgb[0] = a2.x; in.g_rgb[1] = a2.y; in.g_rgb[2] = a2.z;
+  }
   in.clamped = __float_as_uint(gC.w);
 
   const float mx = __ldg(a.means3D + 3 * idx), my = __ldg(a.means3D + 3 * idx + 1), mz = __ldg(a.means3D + 3 * idx + 2);

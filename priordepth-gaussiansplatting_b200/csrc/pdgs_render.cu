@@ -2,11 +2,26 @@
 // Replaces renderCUDA (forward/backward) of the reference rasterizer (source absent;
 // SURVEY.md 2.3(b) K6/K7, A.7, A.8).
 //
-// One CTA per 16x16 tile, 8 warps, each warp owns an 8x4 pixel patch so that warps
-// terminate early and skip non-overlapping Gaussians independently.  Batches of 256
-// Gaussians are staged in shared memory as three float4 records.  The per-pair alpha is
-// computed by ONE shared function in a fixed operation order so that forward and
-// backward take bit-identical accept/reject decisions.
+// One CTA per 16x16 tile, 8 warps, each warp owns an 8x4 pixel patch.  Batches of 256 list
+// entries are staged in shared memory as three float4 records.  Both kernels are
+// instruction-issue bound (ncu r01b: issue active 87 %), so the design removes instructions:
+//
+//  * Hierarchical culling.  The thread that stages a Gaussian also tests its alpha >= 1/255
+//    footprint (the ellipse 0.5 d^T Q d <= ln(255 o)) against the eight warp patches of the tile
+//    (exact minimum of the quadratic over each 8x4 pixel box, with a conservative margin) and
+//    stores an 8-bit patch mask.  Each warp ballots its bit and visits only the survivors.  A
+//    culled Gaussian would have been rejected by every pixel of the patch, so images, n_contrib
+//    and gradients are unchanged; list positions stay those of the un-culled list.
+//  * Backward in two phases per warp.  Phase 1 (lane = pixel) walks the survivors back to front
+//    and, per (pixel, Gaussian), produces just two scalars: w = alpha*T and z = G*dL/dalpha.  They
+//    go to a per-warp [16 Gaussians][32 pixels] shared-memory panel.  Phase 2 (lane = Gaussian x
+//    pixel half) turns a full panel into ten per-Gaussian sums -- the moments sum z, z dx, z dy,
+//    z dx^2, z dx dy, z dy^2 about the Gaussian's own centre and sum w*dL/dC_c, sum w*dL/dD -- with
+//    plain FMAs and ONE shuffle step, then issues three red.global.add.v4.f32.  The moments are
+//    additive over pixels and tiles; the fused preprocess backward (K8+K9) converts them to
+//    dL/dmean2D, dL/dconic, dL/dopacity.  This replaces fifty shuffles per (warp, Gaussian).
+//  * The per-pair alpha is computed by ONE shared function in a fixed operation order so that
+//    forward and backward take bit-identical accept/reject decisions.
 #include "pdgs_internal.cuh"
 
 namespace pdgs {
@@ -14,7 +29,9 @@ namespace pdgs {
 namespace {
 
 constexpr int RT = 256;  // threads per tile CTA
+constexpr int NWARP = RT / 32;
 constexpr float LOG2E = 1.4426950408889634f;
+constexpr unsigned FULL = 0xffffffffu;
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
@@ -30,13 +47,75 @@ __device__ __forceinline__ float gauss_power(float dx, float dy, float hA, float
 }
 __device__ __forceinline__ float gauss_G(float power) { return ex2_approx(__fmul_rn(power, LOG2E)); }
 
-__device__ __forceinline__ void pixel_of_thread(int& lx, int& ly) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  lx = (warp & 1) * 8 + (lane & 7);
-  ly = (warp >> 1) * 4 + (lane >> 3);
+// Mask of the warp patches (bit = warp index = row*2 + col; 2 columns of 8 px, 4 rows of 4 px) of the
+// tile at (tx0, ty0) that the alpha >= 1/255 footprint of a Gaussian can reach.  Conservative: the
+// threshold carries a margin far above the fp32 error of the per-pixel evaluation, and any
+// non-finite / non-positive-definite input keeps every patch.
+__device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, float B, float C, float o, float tx0,
+                                               float ty0) {
+  const float o255 = 255.0f * o;
+  if (!(o255 >= 0.999f)) return (o255 == o255) ? 0u : 0xFFu;  // alpha < 1/255 everywhere
+  if (!(A > 0.f) || !(C > 0.f)) return 0xFFu;
+  const float tau = fmaf(__logf(o255), 1.002f, 0.02f);
+  const float hA = 0.5f * A, hC = 0.5f * C;
+  const float sx = -B * __fdividef(1.0f, A);  // argmin over dx on a row dy = const:  dx* = sx * dy
+  const float sy = -B * __fdividef(1.0f, C);  // argmin over dy on a column dx = const
+  float x0[2], cx[2], y0[4], cy[4];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    x0[k] = (tx0 + 8.0f * k) - gx;  // pixel-centre box relative to the Gaussian
+    cx[k] = fminf(fmaxf(0.f, x0[k]), x0[k] + 7.0f);
+  }
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    y0[m] = (ty0 + 4.0f * m) - gy;
+    cy[m] = fminf(fmaxf(0.f, y0[m]), y0[m] + 3.0f);
+  }
+  uint32_t mask = 0;
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      // the box minimum of a convex quadratic centred outside the box lies on an edge facing the centre
+      const float dyv = fminf(fmaxf(sy * cx[k], y0[m]), y0[m] + 3.0f);
+      const float t1 = hA * cx[k] * cx[k], t2 = B * cx[k] * dyv, t3 = hC * dyv * dyv;
+      const float q1 = (t1 + t2 + t3) - 1e-5f * (t1 + fabsf(t2) + t3);
+      const float dxv = fminf(fmaxf(sx * cy[m], x0[k]), x0[k] + 7.0f);
+      const float u1 = hA * dxv * dxv, u2 = B * dxv * cy[m], u3 = hC * cy[m] * cy[m];
+      const float q2 = (u1 + u2 + u3) - 1e-5f * (u1 + fabsf(u2) + u3);
+      if (!(fminf(q1, q2) > tau)) mask |= 1u << (m * 2 + k);
+    }
+  }
+  return mask;
 }
 
-__global__ void __launch_bounds__(RT) render_forward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
+struct Stage {
+  float4 a[RT];     // x, y, -0.5*conA, -conB
+  float4 b[RT];     // -0.5*conC, opacity, 1/depth, -
+  float4 c[RT];     // r, g, b
+  uint32_t id[RT];  // Gaussian index (backward only)
+  uint32_t mask[RT];
+};
+
+// Stage list entry `src` (or nothing when !valid) into slot threadIdx.x.
+template <bool WITH_ID>
+__device__ __forceinline__ void stage_entry(Stage& st, bool valid, uint32_t src, const float4* __restrict__ gA,
+                                            const float4* __restrict__ gB, const float4* __restrict__ gC,
+                                            const uint32_t* __restrict__ point_list, float tx0, float ty0) {
+  uint32_t m = 0;
+  if (valid) {
+    const uint32_t id = point_list[src];
+    const float4 a = __ldg(gA + id), b = __ldg(gB + id);
+    st.a[threadIdx.x] = make_float4(a.x, a.y, -0.5f * a.z, -a.w);
+    st.b[threadIdx.x] = make_float4(-0.5f * b.x, b.y, b.z, 0.f);
+    st.c[threadIdx.x] = __ldg(gC + id);
+    if (WITH_ID) st.id[threadIdx.x] = id;
+    m = patch_mask(a.x, a.y, a.z, a.w, b.x, b.y, tx0, ty0);
+  }
+  st.mask[threadIdx.x] = m;
+}
+
+__global__ void __launch_bounds__(RT, 4) render_forward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
                                                             const float4* __restrict__ gC,
                                                             const uint2* __restrict__ ranges,
                                                             const uint32_t* __restrict__ point_list, int W, int H,
@@ -45,60 +124,60 @@ __global__ void __launch_bounds__(RT) render_forward_kernel(const float4* __rest
                                                             uint32_t* __restrict__ n_contrib,
                                                             uint32_t* __restrict__ n_tested,
                                                             uint32_t* __restrict__ n_accepted) {
-  __shared__ float4 sA[RT];  // x, y, -0.5*conA, -conB
-  __shared__ float4 sB[RT];  // -0.5*conC, opacity, 1/depth, -
-  __shared__ float4 sC[RT];  // r, g, b
-  int lx, ly;
-  pixel_of_thread(lx, ly);
-  const int px = blockIdx.x * TILE + lx, py = blockIdx.y * TILE + ly;
+  __shared__ Stage st;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int px = blockIdx.x * TILE + (warp & 1) * 8 + (lane & 7);
+  const int py = blockIdx.y * TILE + (warp >> 1) * 4 + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
+  const float tx0 = (float)(blockIdx.x * TILE), ty0 = (float)(blockIdx.y * TILE);
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+  const uint32_t wbit = 1u << warp;
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
-  uint32_t contributor = 0, last = 0, accepted = 0;
+  uint32_t last = 0, accepted = 0, tested = range.y - range.x;
   bool done = !inside;
   for (uint32_t base = range.x; base < range.y; base += RT) {
     if (__syncthreads_count(done) == RT) break;
-    const uint32_t i = base + threadIdx.x;
-    if (i < range.y) {
-      const uint32_t id = point_list[i];
-      const float4 a = __ldg(gA + id), b = __ldg(gB + id);
-      sA[threadIdx.x] = make_float4(a.x, a.y, -0.5f * a.z, -a.w);
-      sB[threadIdx.x] = make_float4(-0.5f * b.x, b.y, b.z, 0.f);
-      sC[threadIdx.x] = __ldg(gC + id);
-    }
+    stage_entry<false>(st, base + threadIdx.x < range.y, base + threadIdx.x, gA, gB, gC, point_list, tx0, ty0);
     __syncthreads();
+    if (__all_sync(FULL, done)) continue;  // this warp's patch is finished; it only helps staging
     const int cnt = min((uint32_t)RT, range.y - base);
-    for (int j = 0; !done && j < cnt; ++j) {
-      ++contributor;
-      const float4 a = sA[j];
-      const float4 b = sB[j];
-      const float dx = a.x - pxf, dy = a.y - pyf;
-      const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-      if (power > 0.0f) continue;
-      const float alpha = fminf(ALPHA_MAX, __fmul_rn(b.y, gauss_G(power)));
-      if (alpha < ALPHA_MIN) continue;
-      const float test_T = T * (1.0f - alpha);
-      if (test_T < T_EPS) {
-        done = true;
-        continue;
+    const uint32_t pos0 = base - range.x;
+    for (int k = 0; k * 32 < cnt; ++k) {
+      uint32_t mw = __ballot_sync(FULL, (st.mask[k * 32 + lane] & wbit) != 0);
+      while (mw) {
+        const int j = k * 32 + __ffs(mw) - 1;
+        mw &= mw - 1;
+        const float4 a = st.a[j];
+        const float4 b = st.b[j];
+        const float dx = a.x - pxf, dy = a.y - pyf;
+        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
+        const float alpha = fminf(ALPHA_MAX, __fmul_rn(b.y, gauss_G(power)));
+        if (done || power > 0.0f || alpha < ALPHA_MIN) continue;
+        const float test_T = T * (1.0f - alpha);
+        if (test_T < T_EPS) {
+          done = true;
+          tested = pos0 + j + 1;
+          continue;
+        }
+        const float4 c = st.c[j];
+        const float w = alpha * T;
+        C0 = fmaf(c.x, w, C0);
+        C1 = fmaf(c.y, w, C1);
+        C2 = fmaf(c.z, w, C2);
+        D = fmaf(b.z, w, D);
+        T = test_T;
+        last = pos0 + j + 1;
+        ++accepted;
       }
-      const float4 c = sC[j];
-      const float w = alpha * T;
-      C0 = fmaf(c.x, w, C0);
-      C1 = fmaf(c.y, w, C1);
-      C2 = fmaf(c.z, w, C2);
-      D = fmaf(b.z, w, D);
-      T = test_T;
-      last = contributor;
-      ++accepted;
+      if (__all_sync(FULL, done)) break;
     }
   }
   if (inside) {
     const size_t pix = (size_t)py * W + px, hw = (size_t)W * H;
     final_T[pix] = T;
     n_contrib[pix] = last;
-    n_tested[pix] = contributor;
+    n_tested[pix] = tested;      // list entries a pixel-serial walk evaluates before this pixel stops
     n_accepted[pix] = accepted;
     out_color[pix] = C0 + T * __ldg(bg + 0);
     out_color[hw + pix] = C1 + T * __ldg(bg + 1);
@@ -107,36 +186,93 @@ __global__ void __launch_bounds__(RT) render_forward_kernel(const float4* __rest
   }
 }
 
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-__global__ void __launch_bounds__(RT) render_backward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
-                                                             const float4* __restrict__ gC,
-                                                             const uint2* __restrict__ ranges,
-                                                             const uint32_t* __restrict__ point_list, int W, int H,
-                                                             const float* __restrict__ bg,
-                                                             const float* __restrict__ final_T,
-                                                             const uint32_t* __restrict__ n_contrib,
-                                                             const float* __restrict__ dL_dcolor,
-                                                             const float* __restrict__ dL_dinvdepth,
-                                                             float* __restrict__ acc) {
-  __shared__ float4 sA[RT];
-  __shared__ float4 sB[RT];
-  __shared__ float4 sC[RT];
-  __shared__ uint32_t sId[RT];
-  __shared__ uint32_t s_max[RT / 32];
-  int lx, ly;
-  pixel_of_thread(lx, ly);
-  const int px = blockIdx.x * TILE + lx, py = blockIdx.y * TILE + ly;
+constexpr int FB = 16;        // Gaussians per phase-2 panel
+constexpr int PANEL_LD = 33;  // float2 row stride: conflict-free for lane = pixel (write) and lane = Gaussian (read)
+
+struct WarpPanel {
+  float2 zw[FB][PANEL_LD];  // (z, w) per (Gaussian slot, pixel lane)
+  float4 gpix[32];          // dL/dC rgb, dL/dD of the warp's pixels
+  float gx[FB], gy[FB];
+  uint32_t id[FB];
+};
+
+struct BwdShared {
+  Stage st;
+  WarpPanel panel[NWARP];
+  uint32_t s_max[NWARP];
+};
+
+// Phase 2: reduce `count` panel rows to per-Gaussian sums and add them to the global accumulator.
+__device__ __forceinline__ void flush_panel(WarpPanel& wp, int count, int lane, float X0f, float Y0f,
+                                            float* __restrict__ acc) {
+  __syncwarp();
+  const int g = lane & (FB - 1), half = lane >> 4;
+  float Sz = 0.f, Szx = 0.f, Szy = 0.f, Szxx = 0.f, Szxy = 0.f, Szyy = 0.f, Sw0 = 0.f, Sw1 = 0.f, Sw2 = 0.f, Swd = 0.f;
+  if (g < count) {
+    const float bx = wp.gx[g] - X0f;                        // dx of pixel column 0 of the patch
+    const float by = (wp.gy[g] - Y0f) - (float)(2 * half);  // dy of the first pixel row of this half
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int p = half * 16 + i;
+      const float2 zw = wp.zw[g][p];
+      const float4 gp = wp.gpix[p];
+      const float dx = bx - (float)(i & 7), dy = by - (float)(i >> 3);
+      const float zdx = zw.x * dx, zdy = zw.x * dy;
+      Sz += zw.x;
+      Szx += zdx;
+      Szy += zdy;
+      Szxx = fmaf(zdx, dx, Szxx);
+      Szxy = fmaf(zdx, dy, Szxy);
+      Szyy = fmaf(zdy, dy, Szyy);
+      Sw0 = fmaf(zw.y, gp.x, Sw0);
+      Sw1 = fmaf(zw.y, gp.y, Sw1);
+      Sw2 = fmaf(zw.y, gp.z, Sw2);
+      Swd = fmaf(zw.y, gp.w, Swd);
+    }
+  }
+  Sz += __shfl_xor_sync(FULL, Sz, 16);
+  Szx += __shfl_xor_sync(FULL, Szx, 16);
+  Szy += __shfl_xor_sync(FULL, Szy, 16);
+  Szxx += __shfl_xor_sync(FULL, Szxx, 16);
+  Szxy += __shfl_xor_sync(FULL, Szxy, 16);
+  Szyy += __shfl_xor_sync(FULL, Szyy, 16);
+  Sw0 += __shfl_xor_sync(FULL, Sw0, 16);
+  Sw1 += __shfl_xor_sync(FULL, Sw1, 16);
+  Sw2 += __shfl_xor_sync(FULL, Sw2, 16);
+  Swd += __shfl_xor_sync(FULL, Swd, 16);
+  if (half == 0 && g < count) {
+    float* dst = acc + (size_t)wp.id[g] * ACC_FLOATS;
+    red_add_v4(dst, Szx, Szy, Szxx, Szxy);
+    red_add_v4(dst + 4, Szyy, Sz, Swd, 0.f);
+    red_add_v4(dst + 8, Sw0, Sw1, Sw2, 0.f);
+  }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
+                                                                const float4* __restrict__ gC,
+                                                                const uint2* __restrict__ ranges,
+                                                                const uint32_t* __restrict__ point_list, int W, int H,
+                                                                const float* __restrict__ bg,
+                                                                const float* __restrict__ final_T,
+                                                                const uint32_t* __restrict__ n_contrib,
+                                                                const float* __restrict__ dL_dcolor,
+                                                                const float* __restrict__ dL_dinvdepth,
+                                                                float* __restrict__ acc) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BwdShared& sh = *reinterpret_cast<BwdShared*>(smem_raw);
+  Stage& st = sh.st;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  WarpPanel& wp = sh.panel[warp];
+  const int X0 = blockIdx.x * TILE + (warp & 1) * 8, Y0 = blockIdx.y * TILE + (warp >> 1) * 4;
+  const int px = X0 + (lane & 7), py = Y0 + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
+  const float tx0 = (float)(blockIdx.x * TILE), ty0 = (float)(blockIdx.y * TILE);
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   const size_t pix = (size_t)py * W + px, hw = (size_t)W * H;
   const float T_final = inside ? final_T[pix] : 0.f;
@@ -148,85 +284,81 @@ __global__ void __launch_bounds__(RT) render_backward_kernel(const float4* __res
     gp2 = dL_dcolor[2 * hw + pix];
     if (dL_dinvdepth) gpd = dL_dinvdepth[pix];
   }
-  const float bg_dot = __ldg(bg + 0) * gp0 + __ldg(bg + 1) * gp1 + __ldg(bg + 2) * gp2;
-  // the tile only needs list positions below the largest n_contrib of its pixels
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t wmax = __reduce_max_sync(0xffffffffu, last_contributor);
-  if (lane == 0) s_max[warp] = wmax;
+  wp.gpix[lane] = make_float4(gp0, gp1, gp2, gpd);
+  // -T_final * (bg . dL/dC): the background term of dL/dalpha is this times 1/(1-alpha)
+  const float bg_term = -T_final * (__ldg(bg + 0) * gp0 + __ldg(bg + 1) * gp1 + __ldg(bg + 2) * gp2);
+  // the tile only needs list positions below the largest n_contrib of its pixels, each warp below its own
+  const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
+  if (lane == 0) sh.s_max[warp] = wmax;
   __syncthreads();
   uint32_t todo = 0;
 #pragma unroll
-  for (int w = 0; w < RT / 32; ++w) todo = max(todo, s_max[w]);
+  for (int w = 0; w < NWARP; ++w) todo = max(todo, sh.s_max[w]);
   todo = min(todo, range.y - range.x);
+  const uint32_t wbit = 1u << warp;
+  const float X0f = (float)X0, Y0f = (float)Y0;
 
   float T = T_final;
-  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ard = 0.f;          // accum_rec
+  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ard = 0.f;  // accum_rec
   float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f, last_alpha = 0.f;
-  const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
+  int slot = 0;
 
   for (uint32_t done = 0; done < todo; done += RT) {
     __syncthreads();
     const uint32_t progress = done + threadIdx.x;
-    if (progress < todo) {
-      const uint32_t id = point_list[range.x + (todo - 1 - progress)];
-      const float4 a = __ldg(gA + id), b = __ldg(gB + id);
-      sId[threadIdx.x] = id;
-      sA[threadIdx.x] = make_float4(a.x, a.y, -0.5f * a.z, -a.w);
-      sB[threadIdx.x] = make_float4(-0.5f * b.x, b.y, b.z, 0.f);
-      sC[threadIdx.x] = __ldg(gC + id);
-    }
+    stage_entry<true>(st, progress < todo, range.x + (todo - 1 - progress), gA, gB, gC, point_list, tx0, ty0);
     __syncthreads();
     const int cnt = min((uint32_t)RT, todo - done);
-    for (int j = 0; j < cnt; ++j) {
-      const uint32_t pos = todo - 1 - (done + j);  // position of this Gaussian in the tile list
-      const float4 a = sA[j];
-      const float4 b = sB[j];
-      const float dx = a.x - pxf, dy = a.y - pyf;
-      const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-      const float G = gauss_G(power);
-      const float alpha = fminf(ALPHA_MAX, __fmul_rn(b.y, G));
-      const bool active = (pos < last_contributor) && !(power > 0.0f) && !(alpha < ALPHA_MIN);
-      if (!__any_sync(0xffffffffu, active)) continue;
-      float g_mx = 0.f, g_my = 0.f, g_cx = 0.f, g_cy = 0.f, g_cw = 0.f, g_op = 0.f, g_id = 0.f, g_r = 0.f, g_g = 0.f,
-            g_b = 0.f;
-      if (active) {
-        const float4 c = sC[j];
-        T = __fdividef(T, 1.0f - alpha);
-        const float w = alpha * T;
-        float dL_dalpha;
-        ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = c.x;
-        ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = c.y;
-        ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = c.z;
-        ard = last_alpha * ld + (1.f - last_alpha) * ard; ld = b.z;
-        dL_dalpha = (c.x - ar0) * gp0 + (c.y - ar1) * gp1 + (c.z - ar2) * gp2 + (b.z - ard) * gpd;
-        g_r = w * gp0; g_g = w * gp1; g_b = w * gp2; g_id = w * gpd;
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
-        const float dL_dG = b.y * dL_dalpha;
-        const float gdx = G * dx, gdy = G * dy;
-        // conic = (A, B, C) = (-2*a.z, -a.w, -2*b.x)
-        const float A = -2.f * a.z, B = -a.w, Cc = -2.f * b.x;
-        const float dG_ddelx = -gdx * A - gdy * B;
-        const float dG_ddely = -gdy * Cc - gdx * B;
-        g_mx = dL_dG * dG_ddelx * ddelx_dx;
-        g_my = dL_dG * dG_ddely * ddely_dy;
-        g_cx = -0.5f * gdx * dx * dL_dG;
-        g_cy = -0.5f * gdx * dy * dL_dG;
-        g_cw = -0.5f * gdy * dy * dL_dG;
-        g_op = G * dL_dalpha;
-      }
-      g_mx = warp_sum(g_mx); g_my = warp_sum(g_my); g_cx = warp_sum(g_cx); g_cy = warp_sum(g_cy);
-      g_cw = warp_sum(g_cw); g_op = warp_sum(g_op); g_id = warp_sum(g_id);
-      g_r = warp_sum(g_r); g_g = warp_sum(g_g); g_b = warp_sum(g_b);
-      if (lane == 0) {
-        float* dst = acc + (size_t)sId[j] * ACC_FLOATS;
-        red_add_v4(dst, g_mx, g_my, g_cx, g_cy);
-        red_add_v4(dst + 4, g_cw, g_op, g_id, 0.f);
-        red_add_v4(dst + 8, g_r, g_g, g_b, 0.f);
+    const uint32_t top = todo - 1 - done;  // list position of staged entry 0 (entries go back to front)
+    if (top - (uint32_t)(cnt - 1) >= wmax) continue;  // even the deepest staged entry is behind this warp's last one
+    for (int k = 0; k * 32 < cnt; ++k) {
+      uint32_t mw = __ballot_sync(FULL, (st.mask[k * 32 + lane] & wbit) != 0);
+      while (mw) {
+        const int j = k * 32 + __ffs(mw) - 1;
+        mw &= mw - 1;
+        const uint32_t pos = top - (uint32_t)j;
+        if (pos >= wmax) continue;
+        const float4 a = st.a[j];
+        const float4 b = st.b[j];
+        const float dx = a.x - pxf, dy = a.y - pyf;
+        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
+        const float G = gauss_G(power);
+        const float alpha = fminf(ALPHA_MAX, __fmul_rn(b.y, G));
+        const bool active = (pos < last_contributor) && !(power > 0.0f) && !(alpha < ALPHA_MIN);
+        if (!__any_sync(FULL, active)) continue;
+        float z = 0.f, w = 0.f;
+        if (active) {
+          const float4 c = st.c[j];
+          const float inv = __fdividef(1.0f, 1.0f - alpha);
+          T *= inv;
+          w = alpha * T;
+          const float om = 1.f - last_alpha;
+          ar0 = fmaf(last_alpha, lc0, om * ar0); lc0 = c.x;
+          ar1 = fmaf(last_alpha, lc1, om * ar1); lc1 = c.y;
+          ar2 = fmaf(last_alpha, lc2, om * ar2); lc2 = c.z;
+          ard = fmaf(last_alpha, ld, om * ard); ld = b.z;
+          last_alpha = alpha;
+          float dL_dalpha = (c.x - ar0) * gp0;
+          dL_dalpha = fmaf(c.y - ar1, gp1, dL_dalpha);
+          dL_dalpha = fmaf(c.z - ar2, gp2, dL_dalpha);
+          dL_dalpha = fmaf(b.z - ard, gpd, dL_dalpha);
+          dL_dalpha = fmaf(dL_dalpha, T, bg_term * inv);
+          z = G * dL_dalpha;
+        }
+        wp.zw[slot][lane] = make_float2(z, w);
+        if (lane == 0) {
+          wp.gx[slot] = a.x;
+          wp.gy[slot] = a.y;
+          wp.id[slot] = st.id[j];
+        }
+        if (++slot == FB) {
+          flush_panel(wp, FB, lane, X0f, Y0f, acc);
+          slot = 0;
+        }
       }
     }
   }
+  if (slot > 0) flush_panel(wp, slot, lane, X0f, Y0f, acc);
 }
 
 }  // namespace
@@ -244,9 +376,18 @@ cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im,
 cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
                                    const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
   if (a.W <= 0 || a.H <= 0) return cudaSuccess;
+  static bool configured[64] = {};  // opt in to > 48 KB of dynamic shared memory once per device
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    e = cudaFuncSetAttribute(render_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdShared));
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
   dim3 grid(a.grid_x, a.grid_y);
-  render_backward_kernel<<<grid, RT, 0, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, a.W, a.H, a.bg, im.final_T,
-                                             im.n_contrib, dL_dcolor, dL_dinvdepth, acc);
+  render_backward_kernel<<<grid, RT, sizeof(BwdShared), s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, a.W, a.H, a.bg,
+                                                             im.final_T, im.n_contrib, dL_dcolor, dL_dinvdepth, acc);
   return cudaGetLastError();
 }
 

@@ -82,6 +82,7 @@ STAGES = ("preprocess", "scan", "duplicate", "sort", "ranges", "blend_fwd", "bwd
 _lib = None
 _lock = threading.Lock()
 _handles = {}  # (thread id, device index) -> PdgsHandle*
+_timing = {}   # device index -> stage timing enabled (applies to every thread's handle on that device)
 
 
 class PdgsError(RuntimeError):
@@ -126,5 +127,14 @@ def handle(device_index: int):
         out = vp()
         check(lib().pdgs_create(C.byref(out)), "pdgs_create")
         h = out
-        _handles[key] = h
+        with _lock:
+            _handles[key] = h
+        if _timing.get(int(device_index)):
+            check(lib().pdgs_set_stage_timing(h, 1), "pdgs_set_stage_timing")
     return h
+
+
+def device_handles(device_index: int):
+    """Every thread's handle on `device_index` (autograd runs backward on its own thread)."""
+    with _lock:
+        return [h for (_, d), h in _handles.items() if d == int(device_index)]

@@ -341,20 +341,31 @@ def image_counters(geom, binning, image, P: int, W: int, H: int) -> dict:
 
 
 def set_stage_timing(device, enable: bool) -> None:
-    """Turn the library's per-stage CUDA-event timing on/off for this thread's handle on `device`."""
+    """Turn the library's per-stage CUDA-event timing on/off for every thread's handle on `device` (autograd runs
+    backward on its own thread, hence with its own handle)."""
     dev = torch.device(device)
     with torch.cuda.device(dev):
-        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
-        L.check(L.lib().pdgs_set_stage_timing(h, int(bool(enable))), "pdgs_set_stage_timing")
+        idx = dev.index if dev.index is not None else torch.cuda.current_device()
+        L.handle(idx)
+        L._timing[int(idx)] = bool(enable)
+        for h in L.device_handles(idx):
+            L.check(L.lib().pdgs_set_stage_timing(h, int(bool(enable))), "pdgs_set_stage_timing")
 
 
 def stage_times(device) -> dict:
-    """{stage: (summed duration in ms, number of launches of the stage)} since the previous call on `device`
-    (waits for the recorded work)."""
+    """{stage: (summed duration in ms, number of launches of the stage)} since the previous call on `device`,
+    summed over the handles of all threads (waits for the recorded work)."""
     dev = torch.device(device)
+    tot = [0.0] * len(L.STAGES)
+    num = [0] * len(L.STAGES)
     with torch.cuda.device(dev):
-        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
-        buf = (C.c_float * len(L.STAGES))()
-        cnt = (C.c_int32 * len(L.STAGES))()
-        L.check(L.lib().pdgs_stage_times(h, buf, cnt, len(L.STAGES)), "pdgs_stage_times")
-    return {name: (float(buf[i]), int(cnt[i])) for i, name in enumerate(L.STAGES)}
+        idx = dev.index if dev.index is not None else torch.cuda.current_device()
+        L.handle(idx)
+        for h in L.device_handles(idx):
+            buf = (C.c_float * len(L.STAGES))()
+            cnt = (C.c_int32 * len(L.STAGES))()
+            L.check(L.lib().pdgs_stage_times(h, buf, cnt, len(L.STAGES)), "pdgs_stage_times")
+            for i in range(len(L.STAGES)):
+                tot[i] += float(buf[i])
+                num[i] += int(cnt[i])
+    return {name: (tot[i], num[i]) for i, name in enumerate(L.STAGES)}
