@@ -14,7 +14,7 @@
 //    and gradients are unchanged; list positions stay those of the un-culled list.
 //  * Backward in two phases per warp.  Phase 1 (lane = pixel) walks the survivors back to front
 //    and, per (pixel, Gaussian), produces just two scalars: w = alpha*T and z = G*dL/dalpha.  They
-//    go to a per-warp [16 Gaussians][32 pixels] shared-memory panel.  Phase 2 (lane = Gaussian x
+//    go to a per-warp [16 Gaussians][32 pixels] shared-memory panel (XOR-swizzled columns).  Phase 2 (lane = Gaussian x
 //    pixel half) turns a full panel into ten per-Gaussian sums -- the moments sum z, z dx, z dy,
 //    z dx^2, z dx dy, z dy^2 about the Gaussian's own centre and sum w*dL/dC_c, sum w*dL/dD -- with
 //    plain FMAs and ONE shuffle step, then issues three red.global.add.v4.f32.  The moments are
@@ -44,6 +44,11 @@ __device__ __forceinline__ float gauss_power(float dx, float dy, float hA, float
   const float u = __fmaf_rn(hA, dx, __fmul_rn(nB, dy));
   const float v = __fmul_rn(__fmul_rn(hC, dy), dy);
   return __fmaf_rn(dx, u, v);
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
 __device__ __forceinline__ float gauss_G(float power) { return ex2_approx(__fmul_rn(power, LOG2E)); }
 
@@ -89,30 +94,27 @@ __device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, floa
   return mask;
 }
 
-struct Stage {
-  float4 a[RT];     // x, y, -0.5*conA, -conB
-  float4 b[RT];     // -0.5*conC, opacity, 1/depth, -
-  float4 c[RT];     // r, g, b
-  uint32_t id[RT];  // Gaussian index (backward only)
-  uint32_t mask[RT];
+struct Stage {          // 41 bytes per staged list entry
+  float4 a[RT];         // x, y, -0.5*conA, -conB
+  float4 b[RT];         // -0.5*conC, opacity, 1/depth, r
+  float2 c[RT];         // g, b
+  uint8_t mask[RT];     // warp patches the Gaussian can reach
 };
 
 // Stage list entry `src` (or nothing when !valid) into slot threadIdx.x.
-template <bool WITH_ID>
 __device__ __forceinline__ void stage_entry(Stage& st, bool valid, uint32_t src, const float4* __restrict__ gA,
                                             const float4* __restrict__ gB, const float4* __restrict__ gC,
                                             const uint32_t* __restrict__ point_list, float tx0, float ty0) {
   uint32_t m = 0;
   if (valid) {
-    const uint32_t id = point_list[src];
-    const float4 a = __ldg(gA + id), b = __ldg(gB + id);
+    const uint32_t id = __ldg(point_list + src);
+    const float4 a = __ldg(gA + id), b = __ldg(gB + id), c = __ldg(gC + id);
     st.a[threadIdx.x] = make_float4(a.x, a.y, -0.5f * a.z, -a.w);
-    st.b[threadIdx.x] = make_float4(-0.5f * b.x, b.y, b.z, 0.f);
-    st.c[threadIdx.x] = __ldg(gC + id);
-    if (WITH_ID) st.id[threadIdx.x] = id;
+    st.b[threadIdx.x] = make_float4(-0.5f * b.x, b.y, b.z, c.x);
+    st.c[threadIdx.x] = make_float2(c.y, c.z);
     m = patch_mask(a.x, a.y, a.z, a.w, b.x, b.y, tx0, ty0);
   }
-  st.mask[threadIdx.x] = m;
+  st.mask[threadIdx.x] = (uint8_t)m;
 }
 
 __global__ void __launch_bounds__(RT, 4) render_forward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
@@ -138,7 +140,7 @@ __global__ void __launch_bounds__(RT, 4) render_forward_kernel(const float4* __r
   bool done = !inside;
   for (uint32_t base = range.x; base < range.y; base += RT) {
     if (__syncthreads_count(done) == RT) break;
-    stage_entry<false>(st, base + threadIdx.x < range.y, base + threadIdx.x, gA, gB, gC, point_list, tx0, ty0);
+    stage_entry(st, base + threadIdx.x < range.y, base + threadIdx.x, gA, gB, gC, point_list, tx0, ty0);
     __syncthreads();
     if (__all_sync(FULL, done)) continue;  // this warp's patch is finished; it only helps staging
     const int cnt = min((uint32_t)RT, range.y - base);
@@ -160,11 +162,11 @@ __global__ void __launch_bounds__(RT, 4) render_forward_kernel(const float4* __r
           tested = pos0 + j + 1;
           continue;
         }
-        const float4 c = st.c[j];
+        const float2 c = st.c[j];
         const float w = alpha * T;
-        C0 = fmaf(c.x, w, C0);
-        C1 = fmaf(c.y, w, C1);
-        C2 = fmaf(c.z, w, C2);
+        C0 = fmaf(b.w, w, C0);
+        C1 = fmaf(c.x, w, C1);
+        C2 = fmaf(c.y, w, C2);
         D = fmaf(b.z, w, D);
         T = test_T;
         last = pos0 + j + 1;
@@ -190,35 +192,31 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-constexpr int FB = 16;        // Gaussians per phase-2 panel
-constexpr int PANEL_LD = 33;  // float2 row stride: conflict-free for lane = pixel (write) and lane = Gaussian (read)
+constexpr int FB = 16;  // Gaussians per phase-2 panel
 
 struct WarpPanel {
-  float2 zw[FB][PANEL_LD];  // (z, w) per (Gaussian slot, pixel lane)
-  float4 gpix[32];          // dL/dC rgb, dL/dD of the warp's pixels
-  float gx[FB], gy[FB];
-  uint32_t id[FB];
-};
-
-struct BwdShared {
-  Stage st;
-  WarpPanel panel[NWARP];
-  uint32_t s_max[NWARP];
+  float2 zw[FB][32];  // (z, w) of (Gaussian slot g, pixel lane p) at column p ^ g: conflict-free for lane = p and lane = g
+  float4 gpix[32];    // dL/dC rgb, dL/dD of the warp's pixels
+  float2 gxy[FB];     // centre of the slot's Gaussian
+  uint32_t pos[FB];   // its position in point_list
 };
 
 // Phase 2: reduce `count` panel rows to per-Gaussian sums and add them to the global accumulator.
 __device__ __forceinline__ void flush_panel(WarpPanel& wp, int count, int lane, float X0f, float Y0f,
-                                            float* __restrict__ acc) {
+                                            const uint32_t* __restrict__ point_list, float* __restrict__ acc) {
   __syncwarp();
   const int g = lane & (FB - 1), half = lane >> 4;
+  uint32_t id = 0;
+  if (half == 0 && g < count) id = __ldg(point_list + wp.pos[g]);  // staged a moment ago: an L1/L2 hit, used last
   float Sz = 0.f, Szx = 0.f, Szy = 0.f, Szxx = 0.f, Szxy = 0.f, Szyy = 0.f, Sw0 = 0.f, Sw1 = 0.f, Sw2 = 0.f, Swd = 0.f;
   if (g < count) {
-    const float bx = wp.gx[g] - X0f;                        // dx of pixel column 0 of the patch
-    const float by = (wp.gy[g] - Y0f) - (float)(2 * half);  // dy of the first pixel row of this half
+    const float2 gxy = wp.gxy[g];
+    const float bx = gxy.x - X0f;                        // dx of pixel column 0 of the patch
+    const float by = (gxy.y - Y0f) - (float)(2 * half);  // dy of the first pixel row of this half
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       const int p = half * 16 + i;
-      const float2 zw = wp.zw[g][p];
+      const float2 zw = wp.zw[g][p ^ g];
       const float4 gp = wp.gpix[p];
       const float dx = bx - (float)(i & 7), dy = by - (float)(i >> 3);
       const float zdx = zw.x * dx, zdy = zw.x * dy;
@@ -245,7 +243,7 @@ __device__ __forceinline__ void flush_panel(WarpPanel& wp, int count, int lane, 
   Sw2 += __shfl_xor_sync(FULL, Sw2, 16);
   Swd += __shfl_xor_sync(FULL, Swd, 16);
   if (half == 0 && g < count) {
-    float* dst = acc + (size_t)wp.id[g] * ACC_FLOATS;
+    float* dst = acc + (size_t)id * ACC_FLOATS;
     red_add_v4(dst, Szx, Szy, Szxx, Szxy);
     red_add_v4(dst + 4, Szyy, Sz, Swd, 0.f);
     red_add_v4(dst + 8, Sw0, Sw1, Sw2, 0.f);
@@ -263,11 +261,12 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
                                                                 const float* __restrict__ dL_dcolor,
                                                                 const float* __restrict__ dL_dinvdepth,
                                                                 float* __restrict__ acc) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  BwdShared& sh = *reinterpret_cast<BwdShared*>(smem_raw);
-  Stage& st = sh.st;
+  __shared__ Stage st;
+  __shared__ WarpPanel panels[NWARP];
+  __shared__ uint32_t s_max[NWARP];
+  static_assert(sizeof(Stage) + NWARP * sizeof(WarpPanel) + NWARP * 4 <= 48 * 1024, "static shared memory budget");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  WarpPanel& wp = sh.panel[warp];
+  WarpPanel& wp = panels[warp];
   const int X0 = blockIdx.x * TILE + (warp & 1) * 8, Y0 = blockIdx.y * TILE + (warp >> 1) * 4;
   const int px = X0 + (lane & 7), py = Y0 + (lane >> 3);
   const bool inside = px < W && py < H;
@@ -289,11 +288,11 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
   const float bg_term = -T_final * (__ldg(bg + 0) * gp0 + __ldg(bg + 1) * gp1 + __ldg(bg + 2) * gp2);
   // the tile only needs list positions below the largest n_contrib of its pixels, each warp below its own
   const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
-  if (lane == 0) sh.s_max[warp] = wmax;
+  if (lane == 0) s_max[warp] = wmax;
   __syncthreads();
   uint32_t todo = 0;
 #pragma unroll
-  for (int w = 0; w < NWARP; ++w) todo = max(todo, sh.s_max[w]);
+  for (int w = 0; w < NWARP; ++w) todo = max(todo, s_max[w]);
   todo = min(todo, range.y - range.x);
   const uint32_t wbit = 1u << warp;
   const float X0f = (float)X0, Y0f = (float)Y0;
@@ -306,7 +305,7 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
   for (uint32_t done = 0; done < todo; done += RT) {
     __syncthreads();
     const uint32_t progress = done + threadIdx.x;
-    stage_entry<true>(st, progress < todo, range.x + (todo - 1 - progress), gA, gB, gC, point_list, tx0, ty0);
+    stage_entry(st, progress < todo, range.x + (todo - 1 - progress), gA, gB, gC, point_list, tx0, ty0);
     __syncthreads();
     const int cnt = min((uint32_t)RT, todo - done);
     const uint32_t top = todo - 1 - done;  // list position of staged entry 0 (entries go back to front)
@@ -328,37 +327,36 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
         if (!__any_sync(FULL, active)) continue;
         float z = 0.f, w = 0.f;
         if (active) {
-          const float4 c = st.c[j];
-          const float inv = __fdividef(1.0f, 1.0f - alpha);
+          const float2 c = st.c[j];
+          const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
           T *= inv;
           w = alpha * T;
           const float om = 1.f - last_alpha;
-          ar0 = fmaf(last_alpha, lc0, om * ar0); lc0 = c.x;
-          ar1 = fmaf(last_alpha, lc1, om * ar1); lc1 = c.y;
-          ar2 = fmaf(last_alpha, lc2, om * ar2); lc2 = c.z;
+          ar0 = fmaf(last_alpha, lc0, om * ar0); lc0 = b.w;
+          ar1 = fmaf(last_alpha, lc1, om * ar1); lc1 = c.x;
+          ar2 = fmaf(last_alpha, lc2, om * ar2); lc2 = c.y;
           ard = fmaf(last_alpha, ld, om * ard); ld = b.z;
           last_alpha = alpha;
-          float dL_dalpha = (c.x - ar0) * gp0;
-          dL_dalpha = fmaf(c.y - ar1, gp1, dL_dalpha);
-          dL_dalpha = fmaf(c.z - ar2, gp2, dL_dalpha);
+          float dL_dalpha = (b.w - ar0) * gp0;
+          dL_dalpha = fmaf(c.x - ar1, gp1, dL_dalpha);
+          dL_dalpha = fmaf(c.y - ar2, gp2, dL_dalpha);
           dL_dalpha = fmaf(b.z - ard, gpd, dL_dalpha);
           dL_dalpha = fmaf(dL_dalpha, T, bg_term * inv);
           z = G * dL_dalpha;
         }
-        wp.zw[slot][lane] = make_float2(z, w);
+        wp.zw[slot][lane ^ slot] = make_float2(z, w);
         if (lane == 0) {
-          wp.gx[slot] = a.x;
-          wp.gy[slot] = a.y;
-          wp.id[slot] = st.id[j];
+          wp.gxy[slot] = make_float2(a.x, a.y);
+          wp.pos[slot] = range.x + pos;
         }
         if (++slot == FB) {
-          flush_panel(wp, FB, lane, X0f, Y0f, acc);
+          flush_panel(wp, FB, lane, X0f, Y0f, point_list, acc);
           slot = 0;
         }
       }
     }
   }
-  if (slot > 0) flush_panel(wp, slot, lane, X0f, Y0f, acc);
+  if (slot > 0) flush_panel(wp, slot, lane, X0f, Y0f, point_list, acc);
 }
 
 }  // namespace
@@ -376,17 +374,8 @@ cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im,
 cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
                                    const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
   if (a.W <= 0 || a.H <= 0) return cudaSuccess;
-  static bool configured[64] = {};  // opt in to > 48 KB of dynamic shared memory once per device
-  int dev = 0;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return e;
-  if (dev < 0 || dev >= 64 || !configured[dev]) {
-    e = cudaFuncSetAttribute(render_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdShared));
-    if (e != cudaSuccess) return e;
-    if (dev >= 0 && dev < 64) configured[dev] = true;
-  }
   dim3 grid(a.grid_x, a.grid_y);
-  render_backward_kernel<<<grid, RT, sizeof(BwdShared), s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, a.W, a.H, a.bg,
+  render_backward_kernel<<<grid, RT, 0, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, a.W, a.H, a.bg,
                                                              im.final_T, im.n_contrib, dL_dcolor, dL_dinvdepth, acc);
   return cudaGetLastError();
 }
