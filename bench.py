@@ -336,13 +336,18 @@ def main():
     nv = max(work["views"], 1)
     Pn, V, R = work["P"], work["V"] / nv, work["R"] / nv
     T, HW = work["tiles"], work["HW"]
-    npass = (32 + max(1, T.bit_length()) + 7) // 8
-    alg = {  # algorithmic bytes / flops per launch (= per view), SURVEY.md 8(d)
-        "preprocess": ("hbm", 12 * Pn + 224 * V + 8 * Pn + 40 * V),
-        "scan": ("hbm", 8 * Pn),
-        "duplicate": ("hbm", 4 * Pn + 16 * V + 12 * R),
-        "sort": ("hbm", 8 * R + npass * 24 * R),
-        "ranges": ("hbm", 8 * R + 8 * T),
+    npass = (max(1, T.bit_length()) + 7) // 8  # tile-id radix passes (8-bit digits); the depth sort always takes 4
+    # Algorithmic bytes / flops per launch (= per view) of THIS pipeline.  Binning is
+    # "depth sort of P Gaussians (u32 key, u32 index) -> scan/duplicate in depth order -> tile-id sort of R pairs
+    # (u32, u32)", which yields the reference's sorted list from 8-byte instead of 12-byte pairs and 2 instead of 6
+    # passes over R; SURVEY.md 8(d)'s figure for the reference's single 64-bit sort is 152 R.
+    alg = {
+        "preprocess": ("hbm", 12 * Pn + 224 * V + 12 * Pn + 40 * V),
+        "depth_sort": ("hbm", 4 * Pn + 12 * Pn + 3 * 16 * Pn),
+        "scan": ("hbm", 12 * Pn),
+        "duplicate": ("hbm", 8 * Pn + 20 * V + 8 * R),
+        "sort": ("hbm", 4 * R + npass * 16 * R),
+        "ranges": ("hbm", 4 * R + 8 * T),
         "blend_fwd": ("fp32_simt", 15 * work["n_test"] / nv + 11 * work["n_acc"] / nv),
         "bwd_zero": ("hbm", 48 * Pn),
         "blend_bwd": ("fp32_simt", 15 * work["n_test_bwd"] / nv + 59 * work["n_acc"] / nv),

@@ -119,7 +119,7 @@ int pdgs_destroy(PdgsHandle* h);
 enum {
   PDGS_STAGE_PREPROCESS = 0, PDGS_STAGE_SCAN = 1, PDGS_STAGE_DUPLICATE = 2, PDGS_STAGE_SORT = 3,
   PDGS_STAGE_RANGES = 4, PDGS_STAGE_BLEND_FWD = 5, PDGS_STAGE_BWD_ZERO = 6, PDGS_STAGE_BLEND_BWD = 7,
-  PDGS_STAGE_PREPROCESS_BWD = 8, PDGS_STAGE_LOSS = 9, PDGS_STAGE_COUNT = 10
+  PDGS_STAGE_PREPROCESS_BWD = 8, PDGS_STAGE_LOSS = 9, PDGS_STAGE_DEPTH_SORT = 10, PDGS_STAGE_COUNT = 11
 };
 int pdgs_set_stage_timing(PdgsHandle* h, int32_t enable);
 int pdgs_stage_times(PdgsHandle* h, float* ms_sum, int32_t* counts, int32_t n);
@@ -167,14 +167,16 @@ int pdgs_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, ui
  * state buffers are freed). */
 typedef struct PdgsStateView {
   const uint32_t* point_list;   /* [R] sorted Gaussian ids */
-  const uint64_t* sorted_keys;  /* [R] (tile << 32) | depth bits */
+  const uint32_t* sorted_tiles; /* [R] tile id of each sorted pair; the reference's 64-bit key of pair i is
+                                 *     (sorted_tiles[i] << 32) | bits(conic_opacity[point_list[i]][3]) */
   const uint32_t* ranges;       /* [T,2] */
   const float* final_T;         /* [H*W] */
   const uint32_t* n_contrib;    /* [H*W] */
   const uint32_t* n_tested;     /* [H*W] list entries evaluated by the forward blend */
   const uint32_t* n_accepted;   /* [H*W] list entries blended */
   const uint32_t* tiles_touched;/* [P] */
-  const uint32_t* point_offsets;/* [P] inclusive scan */
+  const uint32_t* point_offsets;/* [P] inclusive scan of tiles_touched taken in depth order */
+  const uint32_t* depth_order;  /* [P] Gaussian indices sorted by (depth bits, index); culled ones last */
   const float* xy;              /* [P,4] (x, y, conic.x, conic.y) */
   const float* conic_opacity;   /* [P,4] (conic.z, opacity, 1/depth, depth) */
   const float* rgb;             /* [P,4] (r, g, b, clamped-bits) */

@@ -1,6 +1,7 @@
-// K2 scan, K3 duplicateWithKeys, K4 onesweep radix sort, K5 identifyTileRanges.
+// K2 scan, K3 duplicateWithKeys, K4 onesweep radix sorts, K5 identifyTileRanges.
 // Replaces cub::DeviceScan::InclusiveSum, duplicateWithKeys, cub::DeviceRadixSort::SortPairs and
-// identifyTileRanges of the reference rasterizer (source absent).
+// identifyTileRanges of the reference rasterizer (source absent) with a
+// pipeline that produces the identical sorted point list and tile ranges from less data movement.
 //
 // All kernels read the pair count R from device memory (Ctrl::num_rendered) and are guarded by
 // the binning capacity, so the host can enqueue them before it knows R (no mid-forward bubble).
@@ -11,24 +12,40 @@ namespace pdgs {
 namespace {
 
 // ------------------------------------------------------------------------------------------
-// K2: single-pass inclusive scan of tiles_touched with decoupled look-back.
-// state word: [63:62] flag (0 empty, 1 aggregate, 2 inclusive prefix), [61:0] value.
+// Binning pipeline ("depth first, then tile").  The reference sorts R 64-bit (tile | depth) keys
+// with R 32-bit values in one radix sort.  The same sorted list comes out of two much smaller
+// sorts, because an LSD radix sort is stable:
+//   1. sort the P Gaussians by their 32 depth bits (4 passes over 8-byte pairs; culled Gaussians
+//      carry key 0xffffffff and end up last), ties keep ascending index;
+//   2. scan tiles_touched in that order and emit the (tile, index) pairs in that order;
+//   3. stable-sort the R pairs by tile id only (bits(T) bits: 2 passes over 8-byte pairs).
+// Pairs of one tile are then ordered by (depth bits, index): exactly the order a stable sort of the
+// reference's keys over an index-ordered duplication produces.
 // ------------------------------------------------------------------------------------------
 constexpr unsigned long long FLAG_AGG = 1ull << 62;
 constexpr unsigned long long FLAG_INC = 2ull << 62;
 constexpr unsigned long long VAL_MASK = (1ull << 62) - 1;
 
-__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
-  return *reinterpret_cast<const volatile unsigned long long*>(p);
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
 }
-__device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) {
-  *reinterpret_cast<volatile unsigned long long*>(p) = v;
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
-  return *reinterpret_cast<const volatile uint32_t*>(p);
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
 }
-__device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
+__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
+// K2: single-pass inclusive scan (decoupled look-back) of tiles_touched taken in depth order:
+// point_offsets[i] = sum_{k <= i} tiles_touched[order[k]].
+// state word: [63:62] flag (0 empty, 1 aggregate, 2 inclusive prefix), [61:0] value.
 __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(GeomView g, int64_t P) {
   __shared__ uint32_t s_tile;
   __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
@@ -39,15 +56,17 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(GeomView g, int64_t 
   const int64_t base = (int64_t)tile * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS];
   if (base + SCAN_ITEMS <= P) {
-    const uint4* src = reinterpret_cast<const uint4*>(g.tiles_touched + base);
+    const uint4* src = reinterpret_cast<const uint4*>(g.order + base);
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS / 4; ++k) {
       const uint4 q = src[k];
       v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w;
     }
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = __ldg(g.tiles_touched + v[k]);
   } else {
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = (base + k < P) ? g.tiles_touched[base + k] : 0u;
+    for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = (base + k < P) ? __ldg(g.tiles_touched + g.order[base + k]) : 0u;
   }
   unsigned long long tsum = 0;
 #pragma unroll
@@ -72,18 +91,18 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(GeomView g, int64_t 
   if (threadIdx.x == 0) {
     unsigned long long excl = 0;
     if (tile == 0) {
-      st_volatile_u64(&g.scan_state[0], FLAG_INC | total);
+      st_relaxed_u64(&g.scan_state[0], FLAG_INC | total);
     } else {
-      st_volatile_u64(&g.scan_state[tile], FLAG_AGG | total);
+      st_relaxed_u64(&g.scan_state[tile], FLAG_AGG | total);
       int64_t t = (int64_t)tile - 1;
       while (true) {
         unsigned long long s;
-        do { s = ld_volatile_u64(&g.scan_state[t]); } while ((s >> 62) == 0ull);
+        do { s = ld_relaxed_u64(&g.scan_state[t]); } while ((s >> 62) == 0ull);
         excl += s & VAL_MASK;
         if ((s >> 62) == 2ull) break;
         --t;
       }
-      st_volatile_u64(&g.scan_state[tile], FLAG_INC | (excl + total));
+      st_relaxed_u64(&g.scan_state[tile], FLAG_INC | (excl + total));
     }
     s_excl = excl;
     const int64_t ntiles = (P + SCAN_TILE - 1) / SCAN_TILE;
@@ -113,28 +132,50 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(GeomView g, int64_t 
 }
 
 // ------------------------------------------------------------------------------------------
-// K3: emit (tile << 32 | depth bits, id) for every tile of every visible rect (y outer, x inner).
+// K3: emit (tile, index) for every tile of every visible rect, Gaussians taken in depth order.
+// Thread i handles sorted position i; rects of more than DUP_SMALL tiles are emitted by the whole warp.
 // ------------------------------------------------------------------------------------------
+constexpr int DUP_SMALL = 12;
+
 __global__ void __launch_bounds__(256) duplicate_kernel(GeomView g, const int32_t* __restrict__ radii, int64_t P,
-                                                        int grid_x, int grid_y, uint64_t* __restrict__ keys,
+                                                        int grid_x, int grid_y, uint32_t* __restrict__ tkeys,
                                                         uint32_t* __restrict__ vals, int64_t capacity) {
-  const uint32_t R = ld_volatile_u32(&g.ctrl->num_rendered);
+  const uint32_t R = ld_relaxed_u32(&g.ctrl->num_rendered);
   if ((int64_t)R > capacity || g.ctrl->overflow) return;
-  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
-  const int radius = radii[idx];
-  if (radius <= 0) return;
-  const float4 a = g.gA[idx];
-  const float depth = g.gB[idx].w;
-  int rx0, ry0, rx1, ry1;
-  tile_rect(a.x, a.y, radius, grid_x, grid_y, rx0, ry0, rx1, ry1);
-  uint32_t off = (idx == 0) ? 0u : g.point_offsets[idx - 1];
-  const uint64_t dbits = (uint64_t)__float_as_uint(depth);
-  for (int y = ry0; y < ry1; ++y) {
-    for (int x = rx0; x < rx1; ++x) {
-      keys[off] = ((uint64_t)(uint32_t)(y * grid_x + x) << 32) | dbits;
-      vals[off] = (uint32_t)idx;
-      ++off;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  uint32_t idx = 0, off = 0;
+  int rx0 = 0, ry0 = 0, rx1 = 0, ry1 = 0;
+  if (i < P) {
+    idx = g.order[i];
+    const int radius = radii[idx];
+    if (radius > 0) {
+      const float4 a = g.gA[idx];
+      tile_rect(a.x, a.y, radius, grid_x, grid_y, rx0, ry0, rx1, ry1);
+      off = (i == 0) ? 0u : g.point_offsets[i - 1];
+    }
+  }
+  const int w = rx1 - rx0;
+  const int count = w * (ry1 - ry0);
+  if (count > 0 && count <= DUP_SMALL) {
+    for (int y = ry0; y < ry1; ++y)
+      for (int x = rx0; x < rx1; ++x) {
+        tkeys[off] = (uint32_t)(y * grid_x + x);
+        vals[off] = idx;
+        ++off;
+      }
+  }
+  unsigned big = __ballot_sync(0xffffffffu, count > DUP_SMALL);
+  while (big) {
+    const int src = __ffs(big) - 1;
+    big &= big - 1;
+    const int bw = __shfl_sync(0xffffffffu, w, src), bcount = __shfl_sync(0xffffffffu, count, src);
+    const int bx0 = __shfl_sync(0xffffffffu, rx0, src), by0 = __shfl_sync(0xffffffffu, ry0, src);
+    const uint32_t boff = __shfl_sync(0xffffffffu, off, src), bidx = __shfl_sync(0xffffffffu, idx, src);
+    for (int k = lane; k < bcount; k += 32) {
+      const int y = by0 + k / bw, x = bx0 + k % bw;
+      tkeys[boff + k] = (uint32_t)(y * grid_x + x);
+      vals[boff + k] = bidx;
     }
   }
 }
@@ -142,24 +183,28 @@ __global__ void __launch_bounds__(256) duplicate_kernel(GeomView g, const int32_
 // ------------------------------------------------------------------------------------------
 // K4: onesweep LSD radix sort, 8-bit digits.  One histogram kernel for all passes, then one
 // chained-scan (decoupled look-back) kernel per pass.  look-back word: [31:30] flag, [29:0] count.
+// Keys are u32 (depth bits / tile ids) inside the rasterizer; the u64 instantiation serves the
+// stand-alone pdgs_sort_pairs entry point.
 // ------------------------------------------------------------------------------------------
 constexpr uint32_t LB_AGG = 1u << 30;
 constexpr uint32_t LB_INC = 2u << 30;
 constexpr uint32_t LB_MASK = (1u << 30) - 1;
 
-__global__ void __launch_bounds__(256) sort_histogram_kernel(const uint64_t* __restrict__ keys, const uint32_t* n_dev,
-                                                             int64_t capacity, int npass, int end_bit, uint32_t* __restrict__ hist) {
+template <typename KeyT>
+__global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restrict__ keys, const uint32_t* n_dev,
+                                                             int64_t n_host, int64_t capacity, int npass, int end_bit,
+                                                             uint32_t* __restrict__ hist) {
   __shared__ uint32_t s_hist[MAX_PASSES * RADIX];
-  const int64_t n = (int64_t)ld_volatile_u32(n_dev);
+  const int64_t n = n_dev ? (int64_t)ld_relaxed_u32(n_dev) : n_host;
   if (n > capacity) return;
   for (int i = threadIdx.x; i < npass * RADIX; i += blockDim.x) s_hist[i] = 0;
   __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const uint64_t k = keys[i];
+    const KeyT k = keys[i];
     for (int p = 0; p < npass; ++p) {
       const int nb = min(RADIX_BITS, end_bit - p * RADIX_BITS);  // the last pass may cover fewer than 8 bits
-      atomicAdd(&s_hist[p * RADIX + (int)((k >> (p * RADIX_BITS)) & ((1u << nb) - 1u))], 1u);
+      atomicAdd(&s_hist[p * RADIX + (int)((uint32_t)(k >> (p * RADIX_BITS)) & ((1u << nb) - 1u))], 1u);
     }
   }
   __syncthreads();
@@ -169,52 +214,48 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const uint64_t* __r
   }
 }
 
-__global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint64_t* __restrict__ keys_in,
+template <typename KeyT, int ITEMS>
+__global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? 4 : 3) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
-                                                                    uint64_t* __restrict__ keys_out,
+                                                                    KeyT* __restrict__ keys_out,
                                                                     uint32_t* __restrict__ vals_out, const uint32_t* n_dev,
-                                                                    int64_t capacity, int pass, uint32_t digit_mask,
-                                                                    const uint32_t* __restrict__ hist, uint32_t* ticket,
-                                                                    uint32_t* lookback) {
-  __shared__ uint64_t s_keys[SORT_TILE];
-  __shared__ uint32_t s_vals[SORT_TILE];
-  __shared__ uint32_t s_wcnt[SORT_THREADS / 32][RADIX];
-  __shared__ uint32_t s_cta_base[RADIX];    // exclusive prefix of CTA digit counts (smem slot of the digit's first key)
-  __shared__ uint32_t s_goff[RADIX];        // global offset of the digit's first key minus its smem slot
-  __shared__ uint32_t s_scan[SORT_THREADS / 32];
+                                                                    int64_t n_host, int64_t capacity, int shift,
+                                                                    uint32_t digit_mask, const uint32_t* __restrict__ hist,
+                                                                    uint32_t* ticket, uint32_t* lookback) {
+  constexpr int TILE_ITEMS = SORT_THREADS * ITEMS;
+  constexpr int NW = SORT_THREADS / 32;
+  __shared__ KeyT s_keys[TILE_ITEMS];
+  __shared__ uint32_t s_vals[TILE_ITEMS];
+  __shared__ uint32_t s_wcnt[NW][RADIX];
+  __shared__ uint32_t s_cta_base[RADIX];  // exclusive prefix of CTA digit counts (smem slot of the digit's first key)
+  __shared__ uint32_t s_goff[RADIX];      // global offset of the digit's first key minus its smem slot
+  __shared__ uint32_t s_scan[NW], s_scan_h[NW];
   __shared__ uint32_t s_tile;
 
-  const int64_t n = (int64_t)ld_volatile_u32(n_dev);
+  const int64_t n = n_dev ? (int64_t)ld_relaxed_u32(n_dev) : n_host;
   if (n > capacity) return;
   if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
-  for (int i = threadIdx.x; i < (SORT_THREADS / 32) * RADIX; i += SORT_THREADS) (&s_wcnt[0][0])[i] = 0;
+  for (int i = threadIdx.x; i < NW * RADIX; i += SORT_THREADS) (&s_wcnt[0][0])[i] = 0;
   __syncthreads();
   const uint32_t tile = s_tile;
-  const int64_t tile_base = (int64_t)tile * SORT_TILE;
+  const int64_t tile_base = (int64_t)tile * TILE_ITEMS;
   if (tile_base >= n) return;
-  const int valid = (int)((n - tile_base < SORT_TILE) ? (n - tile_base) : SORT_TILE);
+  const int valid = (int)((n - tile_base < TILE_ITEMS) ? (n - tile_base) : TILE_ITEMS);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int shift = pass * RADIX_BITS;
 
-  // warp-striped load: warp w owns SORT_ITEMS*32 consecutive pairs, item i of lane l is seg + i*32 + l
-  uint64_t key[SORT_ITEMS];
-  uint32_t val[SORT_ITEMS];
-  uint32_t rank[SORT_ITEMS];
-  const int seg = warp * SORT_ITEMS * 32;
+  // warp-striped load: warp w owns ITEMS*32 consecutive pairs, item i of lane l is seg + i*32 + l
+  KeyT key[ITEMS];
+  uint32_t rank[ITEMS];
+  const int seg = warp * ITEMS * 32;
 #pragma unroll
-  for (int i = 0; i < SORT_ITEMS; ++i) {
+  for (int i = 0; i < ITEMS; ++i) {
     const int local = seg + i * 32 + lane;
-    if (local < valid) {
-      key[i] = keys_in[tile_base + local];
-      val[i] = vals_in[tile_base + local];
-    } else {
-      key[i] = ~0ull;  // padding: forced into the last bin below, excluded from the counts
-      val[i] = 0u;
-    }
+    key[i] = (local < valid) ? keys_in[tile_base + local]
+                             : (KeyT)~(KeyT)0;  // padding: forced into the last bin below, excluded from the counts
   }
   // per-warp stable ranking with match_any
 #pragma unroll
-  for (int i = 0; i < SORT_ITEMS; ++i) {
+  for (int i = 0; i < ITEMS; ++i) {
     const uint32_t d = (seg + i * 32 + lane < valid) ? ((uint32_t)(key[i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
     const unsigned peers = __match_any_sync(0xffffffffu, d);
     const int leader = __ffs(peers) - 1;
@@ -233,19 +274,18 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
   const int d = threadIdx.x;
   uint32_t cnt = 0;
 #pragma unroll
-  for (int w = 0; w < SORT_THREADS / 32; ++w) {
+  for (int w = 0; w < NW; ++w) {
     const uint32_t c = s_wcnt[w][d];
     s_wcnt[w][d] = cnt;
     cnt += c;
   }
-  const uint32_t n_invalid = (uint32_t)(SORT_TILE - valid);
+  const uint32_t n_invalid = (uint32_t)(TILE_ITEMS - valid);
   const uint32_t cnt_valid = cnt - ((d == RADIX - 1) ? n_invalid : 0u);
   // publish the aggregate as early as possible
   uint32_t* my_lb = lookback + (size_t)tile * RADIX + d;
-  if (tile == 0) st_volatile_u32(my_lb, LB_INC | cnt_valid);
-  else st_volatile_u32(my_lb, LB_AGG | cnt_valid);
+  st_relaxed_u32(my_lb, (tile == 0 ? LB_INC : LB_AGG) | cnt_valid);
   // global base of digit d = exclusive prefix over digits of the global histogram
-  const uint32_t hcount = hist[pass * RADIX + d];
+  const uint32_t hcount = hist[d];
   uint32_t inc_c = cnt, inc_h = hcount;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -253,44 +293,52 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
     const uint32_t b = __shfl_up_sync(0xffffffffu, inc_h, o);
     if (lane >= o) { inc_c += a; inc_h += b; }
   }
-  __shared__ uint32_t s_scan_h[SORT_THREADS / 32];
   if (lane == 31) { s_scan[warp] = inc_c; s_scan_h[warp] = inc_h; }
   __syncthreads();
   uint32_t woff_c = 0, woff_h = 0;
 #pragma unroll
-  for (int w = 0; w < SORT_THREADS / 32; ++w) {
+  for (int w = 0; w < NW; ++w) {
     if (w < warp) { woff_c += s_scan[w]; woff_h += s_scan_h[w]; }
   }
-  const uint32_t cta_base = woff_c + inc_c - cnt;       // exclusive over digits (smem slot)
-  const uint32_t gbase = woff_h + inc_h - hcount;       // exclusive over digits (global)
+  const uint32_t cta_base = woff_c + inc_c - cnt;  // exclusive over digits (smem slot)
+  const uint32_t gbase = woff_h + inc_h - hcount;  // exclusive over digits (global)
+  s_cta_base[d] = cta_base;
+  __syncthreads();
+  // scatter the keys into shared memory in sorted order, then fetch the values: neither needs anything from
+  // other CTAs, so both run before the look-back (predecessors get time to publish, the value loads fly meanwhile)
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const uint32_t dd = (seg + i * 32 + lane < valid) ? ((uint32_t)(key[i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
+    const uint32_t slot = s_cta_base[dd] + s_wcnt[warp][dd] + rank[i];
+    s_keys[slot] = key[i];
+    rank[i] = slot;
+  }
+  uint32_t val[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int local = seg + i * 32 + lane;
+    val[i] = (local < valid) ? (vals_in ? vals_in[tile_base + local] : (uint32_t)(tile_base + local)) : 0u;
+  }
   // decoupled look-back for digit d
   uint32_t excl = 0;
   if (tile > 0) {
     int64_t t = (int64_t)tile - 1;
     while (true) {
       uint32_t s;
-      do { s = ld_volatile_u32(lookback + (size_t)t * RADIX + d); } while ((s >> 30) == 0u);
+      do { s = ld_relaxed_u32(lookback + (size_t)t * RADIX + d); } while ((s >> 30) == 0u);
       excl += s & LB_MASK;
       if ((s >> 30) == 2u) break;
       --t;
     }
-    st_volatile_u32(my_lb, LB_INC | ((excl + cnt_valid) & LB_MASK));
+    st_relaxed_u32(my_lb, LB_INC | ((excl + cnt_valid) & LB_MASK));
   }
-  s_cta_base[d] = cta_base;
   s_goff[d] = gbase + excl - cta_base;
-  __syncthreads();
-  // scatter into shared memory in sorted order
 #pragma unroll
-  for (int i = 0; i < SORT_ITEMS; ++i) {
-    const uint32_t dd = (seg + i * 32 + lane < valid) ? ((uint32_t)(key[i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
-    const uint32_t slot = s_cta_base[dd] + s_wcnt[warp][dd] + rank[i];
-    s_keys[slot] = key[i];
-    s_vals[slot] = val[i];
-  }
+  for (int i = 0; i < ITEMS; ++i) s_vals[rank[i]] = val[i];
   __syncthreads();
   // coalesced write-out; padding keys occupy slots >= valid and are dropped
   for (int j = threadIdx.x; j < valid; j += SORT_THREADS) {
-    const uint64_t k = s_keys[j];
+    const KeyT k = s_keys[j];
     const uint32_t dd = (uint32_t)(k >> shift) & digit_mask;
     const uint32_t dst = s_goff[dd] + (uint32_t)j;
     keys_out[dst] = k;
@@ -299,18 +347,18 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_onesweep_kernel(const uint6
 }
 
 // ------------------------------------------------------------------------------------------
-// K5: per-tile [first, last) from the sorted keys.  ranges is zeroed beforehand.
+// K5: per-tile [first, last) from the sorted tile ids.  ranges is zeroed beforehand.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) ranges_kernel(const uint64_t* __restrict__ keys, const uint32_t* n_dev,
+__global__ void __launch_bounds__(256) ranges_kernel(const uint32_t* __restrict__ tkeys, const uint32_t* n_dev,
                                                      int64_t capacity, uint2* __restrict__ ranges) {
-  const int64_t n = (int64_t)ld_volatile_u32(n_dev);
+  const int64_t n = (int64_t)ld_relaxed_u32(n_dev);
   if (n > capacity) return;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const uint32_t t = (uint32_t)(keys[i] >> 32);
+    const uint32_t t = tkeys[i];
     if (i == 0) ranges[t].x = 0;
     else {
-      const uint32_t tp = (uint32_t)(keys[i - 1] >> 32);
+      const uint32_t tp = tkeys[i - 1];
       if (t != tp) {
         ranges[tp].y = (uint32_t)i;
         ranges[t].x = (uint32_t)i;
@@ -329,52 +377,68 @@ cudaError_t launch_scan(GeomView g, int64_t P, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, const int32_t* radii, uint64_t* keys, uint32_t* vals,
+cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, const int32_t* radii, uint32_t* tkeys, uint32_t* vals,
                              int64_t capacity, cudaStream_t s) {
   if (a.P <= 0) return cudaSuccess;
   const unsigned blocks = (unsigned)((a.P + 255) / 256);
-  duplicate_kernel<<<blocks, 256, 0, s>>>(g, radii, a.P, a.grid_x, a.grid_y, keys, vals, capacity);
+  duplicate_kernel<<<blocks, 256, 0, s>>>(g, radii, a.P, a.grid_x, a.grid_y, tkeys, vals, capacity);
   return cudaGetLastError();
 }
 
-cudaError_t launch_sort(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, const uint32_t* n_dev,
-                        int64_t capacity, int npass, int end_bit, void* scratch, cudaStream_t s) {
+template <typename KeyT, int ITEMS>
+static cudaError_t sort_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals_b, bool iota_vals,
+                             const uint32_t* n_dev, int64_t n_host, int64_t capacity, int npass, int end_bit,
+                             void* scratch, cudaStream_t s) {
   if (capacity <= 0 || npass <= 0) return cudaSuccess;
   if (npass > MAX_PASSES) return cudaErrorInvalidValue;
-  SortScratch sc = carve_sort_scratch(scratch, capacity);
+  SortScratch sc = carve_sort_scratch(scratch, capacity, SORT_THREADS * ITEMS, npass);  // callers size for >= npass
   cudaError_t e = cudaMemsetAsync(scratch, 0, sc.zero_bytes, s);
   if (e != cudaSuccess) return e;
-  uint64_t* kin = (npass % 2 == 0) ? keys_a : keys_b;
+  KeyT* kin = (npass % 2 == 0) ? keys_a : keys_b;
   uint32_t* vin = (npass % 2 == 0) ? vals_a : vals_b;
-  uint64_t* kout = (npass % 2 == 0) ? keys_b : keys_a;
+  KeyT* kout = (npass % 2 == 0) ? keys_b : keys_a;
   uint32_t* vout = (npass % 2 == 0) ? vals_b : vals_a;
   int hist_blocks = (int)((capacity + 256 * 16 - 1) / (256 * 16));
   if (hist_blocks > 148 * 8) hist_blocks = 148 * 8;
   if (hist_blocks < 1) hist_blocks = 1;
-  sort_histogram_kernel<<<hist_blocks, 256, 0, s>>>(kin, n_dev, capacity, npass, end_bit, sc.hist);
+  sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(kin, n_dev, n_host, capacity, npass, end_bit, sc.hist);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const unsigned tiles = (unsigned)sc.ntiles;
   for (int p = 0; p < npass; ++p) {
     const int nb = (end_bit - p * RADIX_BITS < RADIX_BITS) ? end_bit - p * RADIX_BITS : RADIX_BITS;
-    sort_onesweep_kernel<<<tiles, SORT_THREADS, 0, s>>>(kin, vin, kout, vout, n_dev, capacity, p, (1u << nb) - 1u, sc.hist,
-                                                         sc.tickets + p, sc.lookback + (size_t)p * sc.ntiles * RADIX);
+    sort_onesweep_kernel<KeyT, ITEMS><<<tiles, SORT_THREADS, 0, s>>>(
+        kin, (p == 0 && iota_vals) ? nullptr : vin, kout, vout, n_dev, n_host, capacity, p * RADIX_BITS, (1u << nb) - 1u,
+        sc.hist + p * RADIX, sc.tickets + p, sc.lookback + (size_t)p * sc.ntiles * RADIX);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    uint64_t* tk = kin; kin = kout; kout = tk;
+    KeyT* tk = kin; kin = kout; kout = tk;
     uint32_t* tv = vin; vin = vout; vout = tv;
   }
   return cudaSuccess;
 }
 
-cudaError_t launch_ranges(const uint64_t* keys, const uint32_t* n_dev, int64_t capacity, uint2* ranges, int tiles,
+cudaError_t launch_sort_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, bool iota_vals,
+                            const uint32_t* n_dev, int64_t n_host, int64_t capacity, int npass, int end_bit,
+                            void* scratch, cudaStream_t s) {
+  return sort_impl<uint32_t, SORT_ITEMS_U32>(keys_a, vals_a, keys_b, vals_b, iota_vals, n_dev, n_host, capacity, npass,
+                                             end_bit, scratch, s);
+}
+
+cudaError_t launch_sort_u64(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, const uint32_t* n_dev,
+                            int64_t capacity, int npass, int end_bit, void* scratch, cudaStream_t s) {
+  return sort_impl<uint64_t, SORT_ITEMS_U64>(keys_a, vals_a, keys_b, vals_b, false, n_dev, 0, capacity, npass, end_bit,
+                                             scratch, s);
+}
+
+cudaError_t launch_ranges(const uint32_t* tkeys, const uint32_t* n_dev, int64_t capacity, uint2* ranges, int tiles,
                           cudaStream_t s) {
   cudaError_t e = cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), s);
   if (e != cudaSuccess) return e;
   if (capacity <= 0) return cudaSuccess;
   int blocks = (int)((capacity + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  ranges_kernel<<<blocks, 256, 0, s>>>(keys, n_dev, capacity, ranges);
+  ranges_kernel<<<blocks, 256, 0, s>>>(tkeys, n_dev, capacity, ranges);
   return cudaGetLastError();
 }
 

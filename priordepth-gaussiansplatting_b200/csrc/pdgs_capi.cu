@@ -130,7 +130,7 @@ size_t pdgs_binning_bytes(int64_t capacity_pairs, int64_t P) {
   return carve_binning(nullptr, capacity_pairs).bytes;
 }
 size_t pdgs_backward_scratch_bytes(int64_t P) { return align_up((size_t)(P > 0 ? P : 1) * ACC_FLOATS * sizeof(float)); }
-size_t pdgs_sort_scratch_bytes(int64_t n) { return carve_sort_scratch(nullptr, n).bytes + 256; }
+size_t pdgs_sort_scratch_bytes(int64_t n) { return carve_sort_scratch(nullptr, n, SORT_THREADS * SORT_ITEMS_U64).bytes + 256; }
 
 static bool aligned16(const void* p) { return (((uintptr_t)p) & 15u) == 0; }
 
@@ -184,8 +184,8 @@ static int run_binning_and_blend(PdgsHandle* h, const DeviceArgs& a, GeomView g,
   BinningView b = carve_binning(st->binning, st->capacity_pairs);
   if (b.bytes > st->binning_bytes) return fail(PDGS_E_INVALID, "binning buffer smaller than pdgs_binning_bytes(capacity)");
   const int tiles = a.grid_x * a.grid_y;
-  const int npass = num_sort_passes(tiles);
-  uint64_t* kin = (npass % 2 == 0) ? b.keys_a : b.keys_b;
+  const int tbits = tile_id_bits(tiles), npass = num_tile_sort_passes(tiles);
+  uint32_t* kin = (npass % 2 == 0) ? b.tkeys_a : b.tkeys_b;
   uint32_t* vin = (npass % 2 == 0) ? b.point_list : b.vals_b;
   {
     StageTimer t(h, PDGS_STAGE_DUPLICATE, s);
@@ -193,12 +193,12 @@ static int run_binning_and_blend(PdgsHandle* h, const DeviceArgs& a, GeomView g,
   }
   {
     StageTimer t(h, PDGS_STAGE_SORT, s);
-    PD_STEP(debug, s, launch_sort(b.keys_a, b.point_list, b.keys_b, b.vals_b, &g.ctrl->num_rendered,
-                                  st->capacity_pairs, npass, npass * RADIX_BITS, b.sort_scratch, s));
+    PD_STEP(debug, s, launch_sort_u32(b.tkeys_a, b.point_list, b.tkeys_b, b.vals_b, false, &g.ctrl->num_rendered, 0,
+                                      st->capacity_pairs, npass, tbits, b.sort_scratch, s));
   }
   {
     StageTimer t(h, PDGS_STAGE_RANGES, s);
-    PD_STEP(debug, s, launch_ranges(b.keys_a, &g.ctrl->num_rendered, st->capacity_pairs, im.ranges, tiles, s));
+    PD_STEP(debug, s, launch_ranges(b.tkeys_a, &g.ctrl->num_rendered, st->capacity_pairs, im.ranges, tiles, s));
   }
   {
     StageTimer t(h, PDGS_STAGE_BLEND_FWD, s);
@@ -228,6 +228,11 @@ int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, P
     {
       StageTimer t(h, PDGS_STAGE_PREPROCESS, s);
       PD_STEP(debug, s, launch_preprocess(a, g, out->radii, s));
+    }
+    {
+      StageTimer t(h, PDGS_STAGE_DEPTH_SORT, s);
+      PD_STEP(debug, s, launch_sort_u32(g.depth_keys, g.order, g.depth_keys_b, g.order_b, true, nullptr, a.P, a.P,
+                                        DEPTH_SORT_PASSES, 32, g.sort_scratch, s));
     }
     {
       StageTimer t(h, PDGS_STAGE_SCAN, s);
@@ -325,7 +330,7 @@ int pdgs_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, ui
   cudaStream_t s = (cudaStream_t)stream;
   const int npass = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
   // the count lives in the last 256 bytes of the scratch
-  SortScratch sc = carve_sort_scratch(scratch, n);
+  SortScratch sc = carve_sort_scratch(scratch, n, SORT_THREADS * SORT_ITEMS_U64);
   uint32_t* cnt = (uint32_t*)((char*)scratch + sc.bytes);
   const uint32_t n32 = (uint32_t)n;
   PD_CUDA(cudaMemcpyAsync(cnt, &n32, 4, cudaMemcpyHostToDevice, s));
@@ -334,7 +339,7 @@ int pdgs_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, ui
     PD_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, s));
     PD_CUDA(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
   }
-  PD_CUDA(launch_sort(keys_out, vals_out, keys_in, vals_in, cnt, n, npass, end_bit, scratch, s));
+  PD_CUDA(launch_sort_u64(keys_out, vals_out, keys_in, vals_in, cnt, n, npass, end_bit, scratch, s));
   return PDGS_OK;
 }
 
@@ -346,7 +351,7 @@ int pdgs_state_view(const PdgsState* state, int64_t P, int32_t width, int32_t he
   if (state->binning) {
     BinningView b = carve_binning(state->binning, state->capacity_pairs);
     view->point_list = b.point_list;
-    view->sorted_keys = b.keys_a;
+    view->sorted_tiles = b.tkeys_a;
   }
   view->ranges = (const uint32_t*)im.ranges;
   view->final_T = im.final_T;
@@ -355,6 +360,7 @@ int pdgs_state_view(const PdgsState* state, int64_t P, int32_t width, int32_t he
   view->n_accepted = im.n_accepted;
   view->tiles_touched = g.tiles_touched;
   view->point_offsets = g.point_offsets;
+  view->depth_order = g.order;
   view->xy = (const float*)g.gA;
   view->conic_opacity = (const float*)g.gB;
   view->rgb = (const float*)g.gC;

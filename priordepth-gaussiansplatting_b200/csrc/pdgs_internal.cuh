@@ -15,8 +15,9 @@ constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
 constexpr int MAX_PASSES = 8;
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 12;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 3072 pairs per CTA
+constexpr int SORT_ITEMS_U32 = 16;  // 4096 pairs per CTA (u32 keys: depth bits, tile ids)
+constexpr int SORT_ITEMS_U64 = 12;  // 3072 pairs per CTA (u64 keys: stand-alone pdgs_sort_pairs)
+constexpr int DEPTH_SORT_PASSES = 4;
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;  // 4096 counts per CTA
@@ -41,10 +42,39 @@ struct GeomView {
   float4* gB;               // (conic.z, opacity*h, 1/depth, depth)
   float4* gC;               // (r, g, b, clamped bits)
   uint32_t* tiles_touched;  // [P]
-  uint32_t* point_offsets;  // [P] inclusive scan
+  uint32_t* depth_keys;     // [P] depth bits (0xffffffff = culled); sorted ascending after the depth sort
+  uint32_t* order;          // [P] Gaussian indices in (depth bits, index) order
+  uint32_t* depth_keys_b;   // [P] ping-pong buffers of the depth sort
+  uint32_t* order_b;        // [P]
+  uint32_t* point_offsets;  // [P] inclusive scan of tiles_touched taken in depth order
   unsigned long long* scan_state;  // [ceil(P/SCAN_TILE)]
+  void* sort_scratch;       // depth-sort histograms / tickets / look-back words
+  size_t sort_scratch_bytes;
   size_t bytes;
 };
+
+struct SortScratch {
+  uint32_t* hist;      // [MAX_PASSES][RADIX] global digit histograms
+  uint32_t* tickets;   // [MAX_PASSES]
+  uint32_t* lookback;  // [MAX_PASSES][ntiles][RADIX]
+  size_t ntiles;
+  size_t bytes;        // whole scratch
+  size_t zero_bytes;   // prefix that must be zeroed before a sort
+};
+
+inline __host__ SortScratch carve_sort_scratch(void* base, int64_t capacity, int tile_items, int npass = MAX_PASSES) {
+  SortScratch s;
+  char* p = (char*)base;
+  size_t off = 0;
+  const size_t cap = (size_t)(capacity > 0 ? capacity : 1);
+  s.ntiles = (cap + tile_items - 1) / tile_items;
+  s.hist = (uint32_t*)(p + off); off += align_up(MAX_PASSES * RADIX * sizeof(uint32_t));
+  s.tickets = (uint32_t*)(p + off); off += align_up(MAX_PASSES * sizeof(uint32_t));
+  s.lookback = (uint32_t*)(p + off); off += align_up((size_t)npass * s.ntiles * RADIX * sizeof(uint32_t));
+  s.bytes = off;
+  s.zero_bytes = off;
+  return s;
+}
 
 inline __host__ GeomView carve_geom(void* base, int64_t P) {
   GeomView v;
@@ -56,9 +86,16 @@ inline __host__ GeomView carve_geom(void* base, int64_t P) {
   v.gB = (float4*)(p + off); off += align_up(Pn * sizeof(float4));
   v.gC = (float4*)(p + off); off += align_up(Pn * sizeof(float4));
   v.tiles_touched = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
+  v.depth_keys = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
+  v.order = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
+  v.depth_keys_b = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
+  v.order_b = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
   v.point_offsets = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
   const size_t nscan = (Pn + SCAN_TILE - 1) / SCAN_TILE;
   v.scan_state = (unsigned long long*)(p + off); off += align_up(nscan * sizeof(unsigned long long));
+  v.sort_scratch = (void*)(p + off);
+  v.sort_scratch_bytes = carve_sort_scratch(nullptr, P, SORT_THREADS * SORT_ITEMS_U32, DEPTH_SORT_PASSES).bytes;
+  off += align_up(v.sort_scratch_bytes);
   v.bytes = off;
   return v;
 }
@@ -87,38 +124,22 @@ inline __host__ ImageView carve_image(void* base, int W, int H) {
   return v;
 }
 
-struct SortScratch {
-  uint32_t* hist;      // [MAX_PASSES][RADIX] global digit histograms
-  uint32_t* tickets;   // [MAX_PASSES]
-  uint32_t* lookback;  // [MAX_PASSES][ntiles][RADIX]
-  size_t ntiles;
-  size_t bytes;        // whole scratch
-  size_t zero_bytes;   // prefix that must be zeroed before a sort
-};
-
-inline __host__ SortScratch carve_sort_scratch(void* base, int64_t capacity) {
-  SortScratch s;
-  char* p = (char*)base;
-  size_t off = 0;
-  const size_t cap = (size_t)(capacity > 0 ? capacity : 1);
-  s.ntiles = (cap + SORT_TILE - 1) / SORT_TILE;
-  s.hist = (uint32_t*)(p + off); off += align_up(MAX_PASSES * RADIX * sizeof(uint32_t));
-  s.tickets = (uint32_t*)(p + off); off += align_up(MAX_PASSES * sizeof(uint32_t));
-  s.lookback = (uint32_t*)(p + off); off += align_up((size_t)MAX_PASSES * s.ntiles * RADIX * sizeof(uint32_t));
-  s.bytes = off;
-  s.zero_bytes = off;
-  return s;
-}
-
 struct BinningView {
   uint32_t* point_list;  // [cap] sorted Gaussian ids (buffer A values)
-  uint64_t* keys_a;      // [cap] sorted keys (buffer A)
-  uint64_t* keys_b;      // [cap]
+  uint32_t* tkeys_a;     // [cap] sorted tile ids (buffer A keys)
+  uint32_t* tkeys_b;     // [cap]
   uint32_t* vals_b;      // [cap]
   void* sort_scratch;
   size_t sort_scratch_bytes;
   size_t bytes;
 };
+
+inline int tile_id_bits(int tiles) {
+  int bits = 0;
+  while ((1 << bits) <= tiles && bits < 31) ++bits;  // index of MSB + 1 (256 -> 9), as the reference trims its keys
+  return bits;
+}
+inline int num_tile_sort_passes(int tiles) { return (tile_id_bits(tiles) + RADIX_BITS - 1) / RADIX_BITS; }
 
 inline __host__ BinningView carve_binning(void* base, int64_t capacity) {
   BinningView v;
@@ -126,10 +147,10 @@ inline __host__ BinningView carve_binning(void* base, int64_t capacity) {
   size_t off = 0;
   const size_t cap = (size_t)(capacity > 0 ? capacity : 1);
   v.point_list = (uint32_t*)(p + off); off += align_up(cap * sizeof(uint32_t));
-  v.keys_a = (uint64_t*)(p + off); off += align_up(cap * sizeof(uint64_t));
-  v.keys_b = (uint64_t*)(p + off); off += align_up(cap * sizeof(uint64_t));
+  v.tkeys_a = (uint32_t*)(p + off); off += align_up(cap * sizeof(uint32_t));
+  v.tkeys_b = (uint32_t*)(p + off); off += align_up(cap * sizeof(uint32_t));
   v.vals_b = (uint32_t*)(p + off); off += align_up(cap * sizeof(uint32_t));
-  SortScratch s = carve_sort_scratch(nullptr, capacity);
+  SortScratch s = carve_sort_scratch(nullptr, capacity, SORT_THREADS * SORT_ITEMS_U32, 4);
   v.sort_scratch = (void*)(p + off);
   v.sort_scratch_bytes = s.bytes;
   off += align_up(s.bytes);
@@ -155,14 +176,18 @@ struct DeviceArgs {
 
 cudaError_t launch_preprocess(const DeviceArgs& a, GeomView g, int32_t* radii, cudaStream_t s);
 cudaError_t launch_scan(GeomView g, int64_t P, cudaStream_t s);
-cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, const int32_t* radii, uint64_t* keys, uint32_t* vals,
+cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, const int32_t* radii, uint32_t* tkeys, uint32_t* vals,
                              int64_t capacity, cudaStream_t s);
-// Sorts pairs (keys_a, vals_a) <-> (keys_b, vals_b); input must sit in A if npass is even, in B if odd;
-// the result always lands in A.  n is read from *n_dev and must be <= capacity.  Key bits [0, end_bit) are
-// significant (npass = ceil(end_bit / 8); the last pass masks its digit to the remaining bits).
-cudaError_t launch_sort(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, const uint32_t* n_dev,
-                        int64_t capacity, int npass, int end_bit, void* scratch, cudaStream_t s);
-cudaError_t launch_ranges(const uint64_t* keys, const uint32_t* n_dev, int64_t capacity, uint2* ranges, int tiles,
+// Stable LSD radix sorts of (key, u32 value) pairs between buffers A and B.  The input must sit in A if npass is
+// even, in B if odd; the result always lands in A.  n is read from *n_dev (or is n_host when n_dev is NULL) and
+// must be <= capacity.  Key bits [0, end_bit) are significant (npass = ceil(end_bit / 8); the last pass masks its
+// digit to the remaining bits).  iota_vals: the input values are the element indices and are not read.
+cudaError_t launch_sort_u32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, bool iota_vals,
+                            const uint32_t* n_dev, int64_t n_host, int64_t capacity, int npass, int end_bit,
+                            void* scratch, cudaStream_t s);
+cudaError_t launch_sort_u64(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, const uint32_t* n_dev,
+                            int64_t capacity, int npass, int end_bit, void* scratch, cudaStream_t s);
+cudaError_t launch_ranges(const uint32_t* tkeys, const uint32_t* n_dev, int64_t capacity, uint2* ranges, int tiles,
                           cudaStream_t s);
 cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
                                   int64_t capacity, float* out_color, float* out_invdepth, cudaStream_t s);
@@ -180,12 +205,5 @@ cudaError_t launch_image_loss(const float* color, const float* target, const flo
                               float* dL_dinvdepth, float* loss, cudaStream_t s);
 cudaError_t launch_mark_visible(const float* means3D, const float* viewmatrix, int64_t P, uint8_t* present,
                                 cudaStream_t s);
-
-inline int num_sort_passes(int tiles) {
-  int bits = 0;
-  while ((1 << bits) <= tiles && bits < 31) ++bits;  // index of MSB + 1 (256 -> 9)
-  int total = 32 + bits;
-  return (total + RADIX_BITS - 1) / RADIX_BITS;
-}
 
 }  // namespace pdgs

@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(DeviceArgs a, G
   if (!vis) {
     radii[idx] = 0;
     g.tiles_touched[idx] = 0;
+    g.depth_keys[idx] = 0xffffffffu;  // sorts behind every visible Gaussian (depth > 0.2 has the sign bit clear)
     return;
   }
   float rgb[3];
@@ -85,6 +86,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(DeviceArgs a, G
   g.gB[idx] = make_float4(go.conC, opacity * go.h, PD_DIV(1.0f, go.depth), go.depth);
   g.gC[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
   radii[idx] = go.radius;
+  g.depth_keys[idx] = __float_as_uint(go.depth);
   g.tiles_touched[idx] = (uint32_t)((go.rx1 - go.rx0) * (go.ry1 - go.ry0));
 }
 

@@ -50,8 +50,8 @@ class PdgsGrads(C.Structure):
 
 
 class PdgsStateView(C.Structure):
-    _fields_ = [("point_list", vp), ("sorted_keys", vp), ("ranges", vp), ("final_T", vp), ("n_contrib", vp), ("n_tested", vp), ("n_accepted", vp),
-                ("tiles_touched", vp), ("point_offsets", vp), ("xy", vp), ("conic_opacity", vp), ("rgb", vp)]
+    _fields_ = [("point_list", vp), ("sorted_tiles", vp), ("ranges", vp), ("final_T", vp), ("n_contrib", vp), ("n_tested", vp), ("n_accepted", vp),
+                ("tiles_touched", vp), ("point_offsets", vp), ("depth_order", vp), ("xy", vp), ("conic_opacity", vp), ("rgb", vp)]
 
 
 # every symbol include/pdgs.h declares: name -> (restype, argtypes)
@@ -77,7 +77,8 @@ SYMBOLS = {
     "pdgs_state_view": (C.c_int, [C.POINTER(PdgsState), C.c_int64, C.c_int32, C.c_int32, C.POINTER(PdgsStateView)]),
 }
 
-STAGES = ("preprocess", "scan", "duplicate", "sort", "ranges", "blend_fwd", "bwd_zero", "blend_bwd", "preprocess_bwd", "loss")
+STAGES = ("preprocess", "scan", "duplicate", "sort", "ranges", "blend_fwd", "bwd_zero", "blend_bwd", "preprocess_bwd", "loss",
+          "depth_sort")
 
 _lib = None
 _lock = threading.Lock()

@@ -57,7 +57,7 @@ def test_version_and_sizes(lib):
     assert l.pdgs_geom_bytes(0) > 0
     assert l.pdgs_image_bytes(256, 256) >= 256 * 256 * 8
     b = l.pdgs_binning_bytes(1 << 20, 1000)
-    assert b >= (1 << 20) * 24
+    assert b >= (1 << 20) * 16  # two (u32 tile id, u32 index) pair buffers
     assert l.pdgs_backward_scratch_bytes(1000) >= 1000 * 48
     assert l.pdgs_sort_scratch_bytes(1 << 20) > 0
 
