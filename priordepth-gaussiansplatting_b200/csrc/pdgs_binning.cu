@@ -88,28 +88,35 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(GeomView g, int64_t 
     if (w < warp) woff += c;
     total += c;
   }
-  if (threadIdx.x == 0) {
+  if (warp == 0) {
+    // warp-parallel decoupled look-back: lane l inspects tile (t - l); stop at the nearest inclusive prefix
     unsigned long long excl = 0;
-    if (tile == 0) {
-      st_relaxed_u64(&g.scan_state[0], FLAG_INC | total);
-    } else {
-      st_relaxed_u64(&g.scan_state[tile], FLAG_AGG | total);
-      int64_t t = (int64_t)tile - 1;
-      while (true) {
-        unsigned long long s;
-        do { s = ld_relaxed_u64(&g.scan_state[t]); } while ((s >> 62) == 0ull);
-        excl += s & VAL_MASK;
-        if ((s >> 62) == 2ull) break;
-        --t;
+    if (lane == 0) st_relaxed_u64(&g.scan_state[tile], (tile == 0 ? FLAG_INC : FLAG_AGG) | total);
+    int64_t t = (int64_t)tile - 1;
+    while (t >= 0) {
+      const int64_t ti = t - lane;
+      unsigned long long sv = FLAG_INC;  // tiles before the first one: inclusive prefix 0
+      if (ti >= 0) {
+        do { sv = ld_relaxed_u64(&g.scan_state[ti]); } while ((sv >> 62) == 0ull);
       }
-      st_relaxed_u64(&g.scan_state[tile], FLAG_INC | (excl + total));
+      const unsigned incmask = __ballot_sync(0xffffffffu, (sv >> 62) == 2ull);
+      const int first = incmask ? (__ffs(incmask) - 1) : 31;
+      unsigned long long val = (lane <= first) ? (sv & VAL_MASK) : 0ull;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+      excl += val;
+      if (incmask) break;
+      t -= 32;
     }
-    s_excl = excl;
-    const int64_t ntiles = (P + SCAN_TILE - 1) / SCAN_TILE;
-    if ((int64_t)tile == ntiles - 1) {
-      const unsigned long long R = excl + total;
-      g.ctrl->num_rendered = (uint32_t)(R > 0xffffffffull ? 0xffffffffull : R);
-      g.ctrl->overflow = (R >= (unsigned long long)MAX_PAIRS) ? 1u : 0u;
+    if (lane == 0) {
+      if (tile != 0) st_relaxed_u64(&g.scan_state[tile], FLAG_INC | (excl + total));
+      s_excl = excl;
+      const int64_t ntiles = (P + SCAN_TILE - 1) / SCAN_TILE;
+      if ((int64_t)tile == ntiles - 1) {
+        const unsigned long long R = excl + total;
+        g.ctrl->num_rendered = (uint32_t)(R > 0xffffffffull ? 0xffffffffull : R);
+        g.ctrl->overflow = (R >= (unsigned long long)MAX_PAIRS) ? 1u : 0u;
+      }
     }
   }
   __syncthreads();
@@ -136,46 +143,57 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(GeomView g, int64_t 
 // Thread i handles sorted position i; rects of more than DUP_SMALL tiles are emitted by the whole warp.
 // ------------------------------------------------------------------------------------------
 constexpr int DUP_SMALL = 12;
+constexpr int DUP_ITEMS = 4;  // sorted positions per thread (independent gathers in flight)
 
-__global__ void __launch_bounds__(256) duplicate_kernel(GeomView g, const int32_t* __restrict__ radii, int64_t P,
-                                                        int grid_x, int grid_y, uint32_t* __restrict__ tkeys,
+__global__ void __launch_bounds__(256) duplicate_kernel(GeomView g, int64_t P, int grid_x, uint32_t* __restrict__ tkeys,
                                                         uint32_t* __restrict__ vals, int64_t capacity) {
   const uint32_t R = ld_relaxed_u32(&g.ctrl->num_rendered);
   if ((int64_t)R > capacity || g.ctrl->overflow) return;
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * DUP_ITEMS;
   const int lane = threadIdx.x & 31;
-  uint32_t idx = 0, off = 0;
-  int rx0 = 0, ry0 = 0, rx1 = 0, ry1 = 0;
-  if (i < P) {
-    idx = g.order[i];
-    const int radius = radii[idx];
-    if (radius > 0) {
-      const float4 a = g.gA[idx];
-      tile_rect(a.x, a.y, radius, grid_x, grid_y, rx0, ry0, rx1, ry1);
-      off = (i == 0) ? 0u : g.point_offsets[i - 1];
+  uint32_t idx[DUP_ITEMS], off[DUP_ITEMS + 1];
+  uint2 rect[DUP_ITEMS];
+  if (i0 + DUP_ITEMS <= P) {
+    const uint4 q = *reinterpret_cast<const uint4*>(g.order + i0);
+    const uint4 o = *reinterpret_cast<const uint4*>(g.point_offsets + i0);
+    idx[0] = q.x; idx[1] = q.y; idx[2] = q.z; idx[3] = q.w;
+    off[1] = o.x; off[2] = o.y; off[3] = o.z; off[4] = o.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < DUP_ITEMS; ++k) {
+      idx[k] = (i0 + k < P) ? g.order[i0 + k] : 0u;
+      off[k + 1] = (i0 + k < P) ? g.point_offsets[i0 + k] : 0u;
     }
   }
-  const int w = rx1 - rx0;
-  const int count = w * (ry1 - ry0);
-  if (count > 0 && count <= DUP_SMALL) {
-    for (int y = ry0; y < ry1; ++y)
-      for (int x = rx0; x < rx1; ++x) {
-        tkeys[off] = (uint32_t)(y * grid_x + x);
-        vals[off] = idx;
-        ++off;
+  off[0] = (i0 == 0 || i0 >= P) ? 0u : g.point_offsets[i0 - 1];
+#pragma unroll
+  for (int k = 0; k < DUP_ITEMS; ++k) rect[k] = (i0 + k < P) ? __ldg(g.rect + idx[k]) : make_uint2(0u, 0u);
+#pragma unroll
+  for (int k = 0; k < DUP_ITEMS; ++k) {
+    const int rx0 = (int)(rect[k].x & 0xffffu), ry0 = (int)(rect[k].x >> 16);
+    const int w = (int)(rect[k].y & 0xffffu) - rx0, hgt = (int)(rect[k].y >> 16) - ry0;
+    const int count = w * hgt;  // 0 for culled Gaussians
+    uint32_t o = off[k];
+    if (count > 0 && count <= DUP_SMALL) {
+      for (int y = ry0; y < ry0 + hgt; ++y)
+        for (int x = rx0; x < rx0 + w; ++x) {
+          tkeys[o] = (uint32_t)(y * grid_x + x);
+          vals[o] = idx[k];
+          ++o;
+        }
+    }
+    unsigned big = __ballot_sync(0xffffffffu, count > DUP_SMALL);
+    while (big) {  // rects of many tiles: the whole warp emits them
+      const int src = __ffs(big) - 1;
+      big &= big - 1;
+      const int bw = __shfl_sync(0xffffffffu, w, src), bcount = __shfl_sync(0xffffffffu, count, src);
+      const int bx0 = __shfl_sync(0xffffffffu, rx0, src), by0 = __shfl_sync(0xffffffffu, ry0, src);
+      const uint32_t boff = __shfl_sync(0xffffffffu, off[k], src), bidx = __shfl_sync(0xffffffffu, idx[k], src);
+      for (int e = lane; e < bcount; e += 32) {
+        const int y = by0 + e / bw, x = bx0 + e % bw;
+        tkeys[boff + e] = (uint32_t)(y * grid_x + x);
+        vals[boff + e] = bidx;
       }
-  }
-  unsigned big = __ballot_sync(0xffffffffu, count > DUP_SMALL);
-  while (big) {
-    const int src = __ffs(big) - 1;
-    big &= big - 1;
-    const int bw = __shfl_sync(0xffffffffu, w, src), bcount = __shfl_sync(0xffffffffu, count, src);
-    const int bx0 = __shfl_sync(0xffffffffu, rx0, src), by0 = __shfl_sync(0xffffffffu, ry0, src);
-    const uint32_t boff = __shfl_sync(0xffffffffu, off, src), bidx = __shfl_sync(0xffffffffu, idx, src);
-    for (int k = lane; k < bcount; k += 32) {
-      const int y = by0 + k / bw, x = bx0 + k % bw;
-      tkeys[boff + k] = (uint32_t)(y * grid_x + x);
-      vals[boff + k] = bidx;
     }
   }
 }
@@ -214,8 +232,24 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restr
   }
 }
 
+// Lanes of the warp holding the same digit.  Built from one ballot per digit bit: MATCH.ANY serialises over the
+// distinct values in the warp (about 100 cycles per instruction per SM with random 8-bit digits, ncu r01h) and
+// was the bottleneck of every pass.
+__device__ __forceinline__ unsigned warp_peers(uint32_t d, int nbits) {
+  unsigned peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < RADIX_BITS; ++b) {
+    if (b < nbits) {
+      const bool bit = (d >> b) & 1u;
+      const unsigned m = __ballot_sync(0xffffffffu, bit);
+      peers &= bit ? m : ~m;
+    }
+  }
+  return peers;
+}
+
 template <typename KeyT, int ITEMS>
-__global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? 4 : 3) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
+__global__ void __launch_bounds__(SORT_THREADS, 3) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     KeyT* __restrict__ keys_out,
                                                                     uint32_t* __restrict__ vals_out, const uint32_t* n_dev,
@@ -242,6 +276,7 @@ __global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? 4 : 3) sor
   if (tile_base >= n) return;
   const int valid = (int)((n - tile_base < TILE_ITEMS) ? (n - tile_base) : TILE_ITEMS);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nbits = (valid == TILE_ITEMS) ? __popc(digit_mask) : RADIX_BITS;  // padding digits (255) need all 8 bits
 
   // warp-striped load: warp w owns ITEMS*32 consecutive pairs, item i of lane l is seg + i*32 + l
   KeyT key[ITEMS];
@@ -253,21 +288,37 @@ __global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? 4 : 3) sor
     key[i] = (local < valid) ? keys_in[tile_base + local]
                              : (KeyT)~(KeyT)0;  // padding: forced into the last bin below, excluded from the counts
   }
-  // per-warp stable ranking with match_any
+  // per-warp stable ranking: peers of every item first (independent MATCH ops), then one shared-memory atomic
+  // per (item, distinct digit) issued back to back -- program order keeps equal digits of later items behind
+  // earlier ones -- and only then the broadcasts that consume the atomics' results
+  constexpr int CH = 8;  // items ranked together (bounds the live registers)
+  static_assert(ITEMS % 4 == 0, "ITEMS must be a multiple of 4");
 #pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const uint32_t d = (seg + i * 32 + lane < valid) ? ((uint32_t)(key[i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
-    const unsigned peers = __match_any_sync(0xffffffffu, d);
-    const int leader = __ffs(peers) - 1;
-    const uint32_t below = __popc(peers & ((1u << lane) - 1u));
-    uint32_t pre = 0;
-    if (lane == leader) {
-      pre = s_wcnt[warp][d];
-      s_wcnt[warp][d] = pre + __popc(peers);
+  for (int c = 0; c < ITEMS; c += CH) {
+    unsigned peers[CH];
+#pragma unroll
+    for (int i = 0; i < CH; ++i) {
+      if (c + i < ITEMS) {
+        const uint32_t d = (seg + (c + i) * 32 + lane < valid) ? ((uint32_t)(key[c + i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
+        peers[i] = warp_peers(d, nbits);
+      }
     }
-    pre = __shfl_sync(0xffffffffu, pre, leader);
-    rank[i] = pre + below;
-    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < CH; ++i) {
+      if (c + i < ITEMS) {
+        const uint32_t d = (seg + (c + i) * 32 + lane < valid) ? ((uint32_t)(key[c + i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
+        rank[c + i] = 0;
+        if (lane == __ffs(peers[i]) - 1) rank[c + i] = atomicAdd(&s_wcnt[warp][d], (uint32_t)__popc(peers[i]));
+        __syncwarp();
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < CH; ++i) {
+      if (c + i < ITEMS) {
+        const uint32_t pre = __shfl_sync(0xffffffffu, rank[c + i], __ffs(peers[i]) - 1);
+        rank[c + i] = pre + __popc(peers[i] & ((1u << lane) - 1u));
+      }
+    }
   }
   __syncthreads();
   // thread d owns digit d: exclusive scan over warps, CTA count
@@ -377,11 +428,12 @@ cudaError_t launch_scan(GeomView g, int64_t P, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, const int32_t* radii, uint32_t* tkeys, uint32_t* vals,
-                             int64_t capacity, cudaStream_t s) {
+cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, uint32_t* tkeys, uint32_t* vals, int64_t capacity,
+                             cudaStream_t s) {
   if (a.P <= 0) return cudaSuccess;
-  const unsigned blocks = (unsigned)((a.P + 255) / 256);
-  duplicate_kernel<<<blocks, 256, 0, s>>>(g, radii, a.P, a.grid_x, a.grid_y, tkeys, vals, capacity);
+  const int64_t per_block = 256 * DUP_ITEMS;
+  const unsigned blocks = (unsigned)((a.P + per_block - 1) / per_block);
+  duplicate_kernel<<<blocks, 256, 0, s>>>(g, a.P, a.grid_x, tkeys, vals, capacity);
   return cudaGetLastError();
 }
 

@@ -163,6 +163,7 @@ static int make_args(const PdgsScene* sc, const PdgsCamera* cam, DeviceArgs& a) 
   a.focal_y = (float)a.H / (2.0f * cam->tanfovy);
   a.scale_modifier = cam->scale_modifier;
   a.grid_x = (a.W + TILE - 1) / TILE; a.grid_y = (a.H + TILE - 1) / TILE;
+  if (a.grid_x > 65535 || a.grid_y > 65535) return fail(PDGS_E_INVALID, "image larger than 65535 tiles per axis");
   a.sh_degree = cam->sh_degree; a.antialiasing = cam->antialiasing ? 1 : 0;
   return PDGS_OK;
 }
@@ -189,7 +190,7 @@ static int run_binning_and_blend(PdgsHandle* h, const DeviceArgs& a, GeomView g,
   uint32_t* vin = (npass % 2 == 0) ? b.point_list : b.vals_b;
   {
     StageTimer t(h, PDGS_STAGE_DUPLICATE, s);
-    PD_STEP(debug, s, launch_duplicate(a, g, radii, kin, vin, st->capacity_pairs, s));
+    PD_STEP(debug, s, launch_duplicate(a, g, kin, vin, st->capacity_pairs, s));
   }
   {
     StageTimer t(h, PDGS_STAGE_SORT, s);

@@ -42,6 +42,7 @@ struct GeomView {
   float4* gB;               // (conic.z, opacity*h, 1/depth, depth)
   float4* gC;               // (r, g, b, clamped bits)
   uint32_t* tiles_touched;  // [P]
+  uint2* rect;              // [P] tile rect (x0 | y0 << 16, x1 | y1 << 16); (0, 0) = culled
   uint32_t* depth_keys;     // [P] depth bits (0xffffffff = culled); sorted ascending after the depth sort
   uint32_t* order;          // [P] Gaussian indices in (depth bits, index) order
   uint32_t* depth_keys_b;   // [P] ping-pong buffers of the depth sort
@@ -86,6 +87,7 @@ inline __host__ GeomView carve_geom(void* base, int64_t P) {
   v.gB = (float4*)(p + off); off += align_up(Pn * sizeof(float4));
   v.gC = (float4*)(p + off); off += align_up(Pn * sizeof(float4));
   v.tiles_touched = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
+  v.rect = (uint2*)(p + off); off += align_up(Pn * sizeof(uint2));
   v.depth_keys = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
   v.order = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
   v.depth_keys_b = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
@@ -176,8 +178,8 @@ struct DeviceArgs {
 
 cudaError_t launch_preprocess(const DeviceArgs& a, GeomView g, int32_t* radii, cudaStream_t s);
 cudaError_t launch_scan(GeomView g, int64_t P, cudaStream_t s);
-cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, const int32_t* radii, uint32_t* tkeys, uint32_t* vals,
-                             int64_t capacity, cudaStream_t s);
+cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, uint32_t* tkeys, uint32_t* vals, int64_t capacity,
+                             cudaStream_t s);
 // Stable LSD radix sorts of (key, u32 value) pairs between buffers A and B.  The input must sit in A if npass is
 // even, in B if odd; the result always lands in A.  n is read from *n_dev (or is n_host when n_dev is NULL) and
 // must be <= capacity.  Key bits [0, end_bit) are significant (npass = ceil(end_bit / 8); the last pass masks its

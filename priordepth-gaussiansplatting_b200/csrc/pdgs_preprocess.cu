@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(DeviceArgs a, G
   if (!vis) {
     radii[idx] = 0;
     g.tiles_touched[idx] = 0;
+    g.rect[idx] = make_uint2(0u, 0u);
     g.depth_keys[idx] = 0xffffffffu;  // sorts behind every visible Gaussian (depth > 0.2 has the sign bit clear)
     return;
   }
@@ -87,6 +88,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(DeviceArgs a, G
   g.gC[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
   radii[idx] = go.radius;
   g.depth_keys[idx] = __float_as_uint(go.depth);
+  g.rect[idx] = make_uint2((uint32_t)go.rx0 | ((uint32_t)go.ry0 << 16), (uint32_t)go.rx1 | ((uint32_t)go.ry1 << 16));
   g.tiles_touched[idx] = (uint32_t)((go.rx1 - go.rx0) * (go.ry1 - go.ry0));
 }
 
