@@ -1,6 +1,7 @@
 // K1 preprocess (forward), fused K8+K9 preprocess backward, K10 mark_visible.
 // Replaces preprocessCUDA / computeCov2DCUDA-backward / preprocessCUDA-backward / checkFrustum
 // of the reference rasterizer (source absent).
+#include "pdgs_async.cuh"
 #include "pdgs_internal.cuh"
 
 namespace pdgs {
@@ -261,6 +262,226 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
   if (gp.max_radii2D) gp.max_radii2D[idx] = max(gp.max_radii2D[idx], radii[idx]);
 }
 
+// ------------------------------------------------------------------------------------------
+// K8+K9 for the SH path, streamed through shared memory with bulk asynchronous copies.
+// The generic kernel above is latency-bound (ncu r01f: 112 registers, 16 warps/SM, long-scoreboard
+// stalls 16 cycles per issue, 43 % of DRAM peak): every thread gathers its own 192-byte SH row and
+// read-modify-writes its own 192-byte gradient row with 16-byte accesses 192 bytes apart.  Here one
+// elected thread moves the CTA's contiguous [256][3M] SH block and [256][12] accumulator block into
+// shared memory with cp.async.bulk (completion on an mbarrier) and the CTA's SH-gradient block goes
+// back with one cp.async.bulk store -- or, when gradients accumulate over views, one
+// cp.reduce.async.bulk .add.f32, so the read half of the read-modify-write happens in L2 and never
+// occupies the SM.  Two CTAs share an SM: one computes while the other's copies are in flight.
+// ------------------------------------------------------------------------------------------
+constexpr int PB_TILE = 256;
+
+struct PbShared {
+  float sh_in[PB_TILE * 48];
+  float sh_out[PB_TILE * 48];
+  float acc_in[PB_TILE * ACC_FLOATS];
+  Camera cam;
+  unsigned long long bar;
+};
+
+struct ShRow {  // SH block of one Gaussian in shared memory
+  const float* p;
+  __device__ __forceinline__ float operator()(int i) const { return p[i]; }
+};
+
+__global__ void __launch_bounds__(PB_TILE, 2) preprocess_backward_sh_kernel(DeviceArgs a, GeomView g,
+                                                                           const int32_t* __restrict__ radii,
+                                                                           const float* __restrict__ acc, GradPtrs gp,
+                                                                           int bulk_ok) {
+  extern __shared__ __align__(128) unsigned char pb_raw[];
+  PbShared& sm = *reinterpret_cast<PbShared*>(pb_raw);
+  load_camera(a, &sm.cam);
+  const Camera& cam = sm.cam;
+  const int tid = threadIdx.x;
+  const int M = a.M, row = 3 * M;  // floats per SH row
+  if (tid == 0) mbar_init(reinterpret_cast<uint64_t*>(&sm.bar), 1);
+  __syncthreads();
+  uint32_t phase = 0;
+  const int64_t ntiles = (a.P + PB_TILE - 1) / PB_TILE;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t t0 = tile * PB_TILE;
+    const int n = (int)((a.P - t0 < PB_TILE) ? (a.P - t0) : PB_TILE);
+    const bool bulk = bulk_ok && n == PB_TILE;  // full tile and 16-byte aligned arrays
+    if (bulk) {
+      if (tid == 0) {
+        const uint32_t sh_bytes = (uint32_t)(PB_TILE * row * sizeof(float)), acc_bytes = PB_TILE * ACC_FLOATS * 4;
+        mbar_expect_tx(reinterpret_cast<uint64_t*>(&sm.bar), sh_bytes + acc_bytes);
+        bulk_g2s(sm.sh_in, a.shs + (size_t)t0 * row, sh_bytes, reinterpret_cast<uint64_t*>(&sm.bar));
+        bulk_g2s(sm.acc_in, acc + (size_t)t0 * ACC_FLOATS, acc_bytes, reinterpret_cast<uint64_t*>(&sm.bar));
+      }
+    } else {
+      for (int i = tid; i < n * row; i += PB_TILE) sm.sh_in[i] = __ldg(a.shs + (size_t)t0 * row + i);
+      for (int i = tid; i < n * ACC_FLOATS; i += PB_TILE) sm.acc_in[i] = __ldg(acc + (size_t)t0 * ACC_FLOATS + i);
+    }
+    // per-thread inputs that are small or already coalesced come straight from global memory
+    const int64_t idx = t0 + tid;
+    const bool in_range = tid < n;
+    const int radius = in_range ? radii[idx] : 0;
+    const bool vis = radius > 0;
+    float mx = 0.f, my = 0.f, mz = 0.f, opacity = 0.f;
+    float cov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, sc[3] = {0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f};
+    float4 gA = make_float4(0.f, 0.f, 0.f, 0.f), gB = gA, gC = gA;
+    if (vis) {
+      mx = __ldg(a.means3D + 3 * idx); my = __ldg(a.means3D + 3 * idx + 1); mz = __ldg(a.means3D + 3 * idx + 2);
+      if (a.cov3D_precomp) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) cov[k] = __ldg(a.cov3D_precomp + 6 * idx + k);
+      } else {
+        sc[0] = __ldg(a.scales + 3 * idx); sc[1] = __ldg(a.scales + 3 * idx + 1); sc[2] = __ldg(a.scales + 3 * idx + 2);
+        const float4 q4 = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+        q[0] = q4.x; q[1] = q4.y; q[2] = q4.z; q[3] = q4.w;
+      }
+      opacity = __ldg(a.opacities + idx);
+      gA = g.gA[idx]; gB = g.gB[idx]; gC = g.gC[idx];
+    }
+    if (tid == 0) bulk_wait_read0();  // the previous tile's bulk store has finished reading sh_out
+    __syncthreads();
+    if (bulk) {
+      mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar), phase);
+      phase ^= 1u;
+    }
+    float* out_row = sm.sh_out + tid * row;
+    if (!vis) {
+      if (gp.shs) {
+        for (int k = 0; k < row; ++k) out_row[k] = 0.f;
+      }
+      if (in_range && !gp.accumulate) {  // dense zero rows for culled Gaussians
+        if (gp.means3D) { gp.means3D[3 * idx] = 0.f; gp.means3D[3 * idx + 1] = 0.f; gp.means3D[3 * idx + 2] = 0.f; }
+        if (gp.means2D) { gp.means2D[3 * idx] = 0.f; gp.means2D[3 * idx + 1] = 0.f; gp.means2D[3 * idx + 2] = 0.f; }
+        if (gp.opacities) gp.opacities[idx] = 0.f;
+        if (gp.scales) { gp.scales[3 * idx] = 0.f; gp.scales[3 * idx + 1] = 0.f; gp.scales[3 * idx + 2] = 0.f; }
+        if (gp.rotations) reinterpret_cast<float4*>(gp.rotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (gp.cov3D_precomp) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k) gp.cov3D_precomp[6 * idx + k] = 0.f;
+        }
+      }
+    } else {
+      const float4* accv = reinterpret_cast<const float4*>(sm.acc_in + tid * ACC_FLOATS);
+      const float4 a0 = accv[0], a1 = accv[1], a2 = accv[2];
+      BwdIn in;
+      {
+        // acc holds the raw pixel moments of z = G*dL/dalpha about the Gaussian's centre (pdgs_render.cu)
+        const float cA = gA.z, cB = gA.w, cC = gB.x, o = gB.y;
+        in.g_mean2d_x = -o * (0.5f * (float)a.W) * (cA * a0.x + cB * a0.y);
+        in.g_mean2d_y = -o * (0.5f * (float)a.H) * (cC * a0.y + cB * a0.x);
+        const float ho = -0.5f * o;
+        in.g_conic_x = ho * a0.z; in.g_conic_y = ho * a0.w; in.g_conic_w = ho * a1.x;
+        in.g_opacity = a1.y; in.g_invdepth = a1.z;
+        in.g_rgb[0] = a2.x; in.g_rgb[1] = a2.y; in.g_rgb[2] = a2.z;
+      }
+      in.clamped = __float_as_uint(gC.w);
+      if (!a.cov3D_precomp) cov3d_from_scale_rot(sc, cam.scale_modifier, q, cov);
+      float g_mean[3], g_op, g_cov[6];
+      geometry_backward(cam, mx, my, mz, cov, opacity, in, g_mean, g_op, g_cov);
+      // colour: dL/dsh rows into shared memory, view-direction term into dL/dmean
+      float grgb[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) grgb[c] = ((in.clamped >> c) & 1u) ? 0.f : in.g_rgb[c];
+      const float dx = mx - cam.campos[0], dy = my - cam.campos[1], dz = mz - cam.campos[2];
+      float gdir[3], basis[16];
+      if (M == 16) {
+        ShRegs sh;
+        const float4* src = reinterpret_cast<const float4*>(sm.sh_in + tid * 48);
+#pragma unroll
+        for (int k = 0; k < 12; ++k) {
+          const float4 v = src[k];
+          sh.v[4 * k] = v.x; sh.v[4 * k + 1] = v.y; sh.v[4 * k + 2] = v.z; sh.v[4 * k + 3] = v.w;
+        }
+        sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
+      } else {
+        ShRow sh{sm.sh_in + tid * row};
+        sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
+      }
+      g_mean[0] += gdir[0]; g_mean[1] += gdir[1]; g_mean[2] += gdir[2];
+      if (gp.shs) {
+        const int ncoef = sh_num_coeffs(cam.sh_degree);
+        if (M == 16) {
+          float out[48];
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const float bk = (k < ncoef) ? basis[k] : 0.f;
+            out[3 * k] = bk * grgb[0]; out[3 * k + 1] = bk * grgb[1]; out[3 * k + 2] = bk * grgb[2];
+          }
+          float4* dst = reinterpret_cast<float4*>(out_row);
+#pragma unroll
+          for (int k = 0; k < 12; ++k) dst[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+        } else {
+          for (int k = 0; k < M; ++k) {
+            const float bk = (k < ncoef) ? basis[k] : 0.f;
+            out_row[3 * k] = bk * grgb[0]; out_row[3 * k + 1] = bk * grgb[1]; out_row[3 * k + 2] = bk * grgb[2];
+          }
+        }
+      }
+      // covariance
+      if (a.cov3D_precomp) {
+        if (gp.cov3D_precomp) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k) {
+            if (gp.accumulate) gp.cov3D_precomp[6 * idx + k] += g_cov[k]; else gp.cov3D_precomp[6 * idx + k] = g_cov[k];
+          }
+        }
+      } else {
+        float g_scale[3], g_rot[4];
+        cov3d_backward(sc, cam.scale_modifier, q, g_cov, g_scale, g_rot);
+        if (gp.scales) {
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            if (gp.accumulate) gp.scales[3 * idx + k] += g_scale[k]; else gp.scales[3 * idx + k] = g_scale[k];
+          }
+        }
+        if (gp.rotations) {
+          float4* dst = reinterpret_cast<float4*>(gp.rotations) + idx;
+          float4 v = make_float4(g_rot[0], g_rot[1], g_rot[2], g_rot[3]);
+          if (gp.accumulate) { const float4 o = *dst; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+          *dst = v;
+        }
+      }
+      if (gp.means3D) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          if (gp.accumulate) gp.means3D[3 * idx + k] += g_mean[k]; else gp.means3D[3 * idx + k] = g_mean[k];
+        }
+      }
+      if (gp.means2D) {
+        if (gp.accumulate) { gp.means2D[3 * idx] += in.g_mean2d_x; gp.means2D[3 * idx + 1] += in.g_mean2d_y; }
+        else { gp.means2D[3 * idx] = in.g_mean2d_x; gp.means2D[3 * idx + 1] = in.g_mean2d_y; gp.means2D[3 * idx + 2] = 0.f; }
+      }
+      if (gp.opacities) {
+        if (gp.accumulate) gp.opacities[idx] += g_op; else gp.opacities[idx] = g_op;
+      }
+      // densification statistics of this view (scene/gaussian_model.py:502-506, train.py:313-314)
+      if (gp.densify_grad_accum)
+        gp.densify_grad_accum[idx] += sqrtf(in.g_mean2d_x * in.g_mean2d_x + in.g_mean2d_y * in.g_mean2d_y);
+      if (gp.densify_denom) gp.densify_denom[idx] += 1.0f;
+      if (gp.max_radii2D) gp.max_radii2D[idx] = max(gp.max_radii2D[idx], radius);
+    }
+    if (gp.shs) {
+      fence_async_smem();  // generic-proxy writes of sh_out -> visible to the bulk store
+      __syncthreads();
+      float* dst = gp.shs + (size_t)t0 * row;
+      if (bulk) {
+        if (tid == 0) {
+          const uint32_t sh_bytes = (uint32_t)(PB_TILE * row * sizeof(float));
+          if (gp.accumulate) bulk_s2g_add_f32(dst, sm.sh_out, sh_bytes); else bulk_s2g(dst, sm.sh_out, sh_bytes);
+          bulk_commit();
+        }
+      } else {
+        for (int i = tid; i < n * row; i += PB_TILE) {
+          if (gp.accumulate) dst[i] += sm.sh_out[i]; else dst[i] = sm.sh_out[i];
+        }
+      }
+    } else {
+      __syncthreads();  // sh_in / acc_in are free for the next tile's copies
+    }
+  }
+  if (tid == 0) bulk_wait0();  // all bulk stores complete before the CTA's shared memory goes away
+}
+
 __global__ void mark_visible_kernel(const float* __restrict__ means3D, const float* __restrict__ viewmatrix, int64_t P,
                                     uint8_t* __restrict__ present) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -284,6 +505,24 @@ cudaError_t launch_preprocess(const DeviceArgs& a, GeomView g, int32_t* radii, c
 cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const int32_t* radii, const float* acc,
                                        GradPtrs gp, cudaStream_t s) {
   if (a.P <= 0) return cudaSuccess;
+  if (a.shs) {  // SH path: bulk-copy pipeline
+    static bool configured[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+      e = cudaFuncSetAttribute(preprocess_backward_sh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)sizeof(PbShared));
+      if (e != cudaSuccess) return e;
+      if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
+    const auto al16 = [](const void* p) { return (((uintptr_t)p) & 15u) == 0; };
+    const int bulk_ok = al16(a.shs) && al16(acc) && (!gp.shs || al16(gp.shs));
+    const int64_t ntiles = (a.P + PB_TILE - 1) / PB_TILE;
+    const unsigned blocks = (unsigned)(ntiles < 2 * 148 ? ntiles : 2 * 148);  // persistent: two CTAs per SM
+    preprocess_backward_sh_kernel<<<blocks, PB_TILE, sizeof(PbShared), s>>>(a, g, radii, acc, gp, bulk_ok);
+    return cudaGetLastError();
+  }
   const unsigned blocks = (unsigned)((a.P + PRE_THREADS - 1) / PRE_THREADS);
   preprocess_backward_kernel<<<blocks, PRE_THREADS, 0, s>>>(a, g, radii, acc, gp);
   return cudaGetLastError();
