@@ -300,7 +300,7 @@ def main():
             tg = {}
             for i in my:
                 vs[i] = settings(scene.views[i], cam_views(cam_host[i].to(dev, non_blocking=True)))
-                tg[i] = tgt_host[i].to(dev, non_blocking=True)
+                tg[i] = tgt_host[i]  # pinned host tensor: step() uploads it one view ahead on a copy stream
             out = vp.step(g, vs, tg)
             return out["loss_sums"].cpu()  # device -> host read of the step's result (synchronises)
 

@@ -140,61 +140,57 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(GeomView g, int64_t 
 
 // ------------------------------------------------------------------------------------------
 // K3: emit (tile, index) for every tile of every visible rect, Gaussians taken in depth order.
-// Thread i handles sorted position i; rects of more than DUP_SMALL tiles are emitted by the whole warp.
+// Output-centric: a warp owns DUP_SEG consecutive sorted Gaussians, whose pairs form ONE contiguous
+// output range; lane l writes output positions l, l+32, ... of that range and finds the owning Gaussian
+// with a binary search over the segment's offsets in shared memory.  Every store is fully coalesced and
+// a rect of thousands of tiles costs the same per pair as a rect of one.
 // ------------------------------------------------------------------------------------------
-constexpr int DUP_SMALL = 12;
-constexpr int DUP_ITEMS = 4;  // sorted positions per thread (independent gathers in flight)
+constexpr int DUP_SEG = 128;  // sorted Gaussians per warp
+constexpr int DUP_WARPS = 8;
 
-__global__ void __launch_bounds__(256) duplicate_kernel(GeomView g, int64_t P, int grid_x, uint32_t* __restrict__ tkeys,
-                                                        uint32_t* __restrict__ vals, int64_t capacity) {
+__global__ void __launch_bounds__(DUP_WARPS * 32) duplicate_kernel(GeomView g, int64_t P, int grid_x,
+                                                                   uint32_t* __restrict__ tkeys,
+                                                                   uint32_t* __restrict__ vals, int64_t capacity) {
+  __shared__ uint32_t s_off[DUP_WARPS][DUP_SEG + 1];
+  __shared__ uint2 s_rect[DUP_WARPS][DUP_SEG];
+  __shared__ uint32_t s_idx[DUP_WARPS][DUP_SEG];
   const uint32_t R = ld_relaxed_u32(&g.ctrl->num_rendered);
   if ((int64_t)R > capacity || g.ctrl->overflow) return;
-  const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * DUP_ITEMS;
-  const int lane = threadIdx.x & 31;
-  uint32_t idx[DUP_ITEMS], off[DUP_ITEMS + 1];
-  uint2 rect[DUP_ITEMS];
-  if (i0 + DUP_ITEMS <= P) {
-    const uint4 q = *reinterpret_cast<const uint4*>(g.order + i0);
-    const uint4 o = *reinterpret_cast<const uint4*>(g.point_offsets + i0);
-    idx[0] = q.x; idx[1] = q.y; idx[2] = q.z; idx[3] = q.w;
-    off[1] = o.x; off[2] = o.y; off[3] = o.z; off[4] = o.w;
-  } else {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t seg0 = ((int64_t)blockIdx.x * DUP_WARPS + warp) * DUP_SEG;
+  if (seg0 >= P) return;
+  const int n = (int)((P - seg0 < DUP_SEG) ? (P - seg0) : DUP_SEG);
+  uint32_t* off = s_off[warp];
+  if (lane == 0) off[0] = (seg0 == 0) ? 0u : g.point_offsets[seg0 - 1];
 #pragma unroll
-    for (int k = 0; k < DUP_ITEMS; ++k) {
-      idx[k] = (i0 + k < P) ? g.order[i0 + k] : 0u;
-      off[k + 1] = (i0 + k < P) ? g.point_offsets[i0 + k] : 0u;
+  for (int k = 0; k < DUP_SEG / 32; ++k) {
+    const int j = k * 32 + lane;
+    if (j < n) {
+      const uint32_t idx = g.order[seg0 + j];
+      off[j + 1] = g.point_offsets[seg0 + j];
+      s_idx[warp][j] = idx;
+      s_rect[warp][j] = __ldg(g.rect + idx);
     }
   }
-  off[0] = (i0 == 0 || i0 >= P) ? 0u : g.point_offsets[i0 - 1];
+  __syncwarp();
+  const uint32_t first = off[0], total = off[n] - first;
+  for (uint32_t e = lane; e < total; e += 32) {
+    const uint32_t pos = first + e;
+    // largest j in [0, n) with off[j] <= pos  (off is non-decreasing; empty Gaussians have off[j] == off[j+1])
+    int lo = 0, hi = n;  // invariant: off[lo] <= pos < off[hi]
 #pragma unroll
-  for (int k = 0; k < DUP_ITEMS; ++k) rect[k] = (i0 + k < P) ? __ldg(g.rect + idx[k]) : make_uint2(0u, 0u);
-#pragma unroll
-  for (int k = 0; k < DUP_ITEMS; ++k) {
-    const int rx0 = (int)(rect[k].x & 0xffffu), ry0 = (int)(rect[k].x >> 16);
-    const int w = (int)(rect[k].y & 0xffffu) - rx0, hgt = (int)(rect[k].y >> 16) - ry0;
-    const int count = w * hgt;  // 0 for culled Gaussians
-    uint32_t o = off[k];
-    if (count > 0 && count <= DUP_SMALL) {
-      for (int y = ry0; y < ry0 + hgt; ++y)
-        for (int x = rx0; x < rx0 + w; ++x) {
-          tkeys[o] = (uint32_t)(y * grid_x + x);
-          vals[o] = idx[k];
-          ++o;
-        }
-    }
-    unsigned big = __ballot_sync(0xffffffffu, count > DUP_SMALL);
-    while (big) {  // rects of many tiles: the whole warp emits them
-      const int src = __ffs(big) - 1;
-      big &= big - 1;
-      const int bw = __shfl_sync(0xffffffffu, w, src), bcount = __shfl_sync(0xffffffffu, count, src);
-      const int bx0 = __shfl_sync(0xffffffffu, rx0, src), by0 = __shfl_sync(0xffffffffu, ry0, src);
-      const uint32_t boff = __shfl_sync(0xffffffffu, off[k], src), bidx = __shfl_sync(0xffffffffu, idx[k], src);
-      for (int e = lane; e < bcount; e += 32) {
-        const int y = by0 + e / bw, x = bx0 + e % bw;
-        tkeys[boff + e] = (uint32_t)(y * grid_x + x);
-        vals[boff + e] = bidx;
+    for (int it = 0; it < 7; ++it) {
+      const int mid = (lo + hi) >> 1;
+      if (hi - lo > 1) {
+        if (off[mid] <= pos) lo = mid; else hi = mid;
       }
     }
+    const uint2 rc = s_rect[warp][lo];
+    const uint32_t rx0 = rc.x & 0xffffu, ry0 = rc.x >> 16, w = (rc.y & 0xffffu) - rx0;
+    const uint32_t local = pos - off[lo];
+    const uint32_t dy = local / w, dx = local - dy * w;
+    tkeys[pos] = (ry0 + dy) * (uint32_t)grid_x + rx0 + dx;
+    vals[pos] = s_idx[warp][lo];
   }
 }
 
@@ -240,16 +236,17 @@ __device__ __forceinline__ unsigned warp_peers(uint32_t d, int nbits) {
 #pragma unroll
   for (int b = 0; b < RADIX_BITS; ++b) {
     if (b < nbits) {
-      const bool bit = (d >> b) & 1u;
+      const bool bit = (d & (1u << b)) != 0u;
       const unsigned m = __ballot_sync(0xffffffffu, bit);
-      peers &= bit ? m : ~m;
+      const unsigned x = bit ? 0xffffffffu : 0u;
+      peers &= ~(m ^ x);  // lanes whose bit b equals mine
     }
   }
   return peers;
 }
 
 template <typename KeyT, int ITEMS>
-__global__ void __launch_bounds__(SORT_THREADS, 3) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
+__global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? 4 : 3) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     KeyT* __restrict__ keys_out,
                                                                     uint32_t* __restrict__ vals_out, const uint32_t* n_dev,
@@ -276,7 +273,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) sort_onesweep_kernel(const Ke
   if (tile_base >= n) return;
   const int valid = (int)((n - tile_base < TILE_ITEMS) ? (n - tile_base) : TILE_ITEMS);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nbits = (valid == TILE_ITEMS) ? __popc(digit_mask) : RADIX_BITS;  // padding digits (255) need all 8 bits
+  const int nbits = __popc(digit_mask);
 
   // warp-striped load: warp w owns ITEMS*32 consecutive pairs, item i of lane l is seg + i*32 + l
   KeyT key[ITEMS];
@@ -286,7 +283,8 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) sort_onesweep_kernel(const Ke
   for (int i = 0; i < ITEMS; ++i) {
     const int local = seg + i * 32 + lane;
     key[i] = (local < valid) ? keys_in[tile_base + local]
-                             : (KeyT)~(KeyT)0;  // padding: forced into the last bin below, excluded from the counts
+                             : (KeyT)~(KeyT)0;  // padding: digit = digit_mask, the last bin in use; ranked behind every real key of that
+                                                // bin (higher local index), so it lands in slots >= valid and is dropped
   }
   // per-warp stable ranking: peers of every item first (independent MATCH ops), then one shared-memory atomic
   // per (item, distinct digit) issued back to back -- program order keeps equal digits of later items behind
@@ -299,14 +297,14 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) sort_onesweep_kernel(const Ke
 #pragma unroll
     for (int i = 0; i < CH; ++i) {
       if (c + i < ITEMS) {
-        const uint32_t d = (seg + (c + i) * 32 + lane < valid) ? ((uint32_t)(key[c + i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
+        const uint32_t d = (uint32_t)(key[c + i] >> shift) & digit_mask;
         peers[i] = warp_peers(d, nbits);
       }
     }
 #pragma unroll
     for (int i = 0; i < CH; ++i) {
       if (c + i < ITEMS) {
-        const uint32_t d = (seg + (c + i) * 32 + lane < valid) ? ((uint32_t)(key[c + i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
+        const uint32_t d = (uint32_t)(key[c + i] >> shift) & digit_mask;
         rank[c + i] = 0;
         if (lane == __ffs(peers[i]) - 1) rank[c + i] = atomicAdd(&s_wcnt[warp][d], (uint32_t)__popc(peers[i]));
         __syncwarp();
@@ -331,7 +329,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) sort_onesweep_kernel(const Ke
     cnt += c;
   }
   const uint32_t n_invalid = (uint32_t)(TILE_ITEMS - valid);
-  const uint32_t cnt_valid = cnt - ((d == RADIX - 1) ? n_invalid : 0u);
+  const uint32_t cnt_valid = cnt - (((uint32_t)d == digit_mask) ? n_invalid : 0u);
   // publish the aggregate as early as possible
   uint32_t* my_lb = lookback + (size_t)tile * RADIX + d;
   st_relaxed_u32(my_lb, (tile == 0 ? LB_INC : LB_AGG) | cnt_valid);
@@ -359,7 +357,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) sort_onesweep_kernel(const Ke
   // other CTAs, so both run before the look-back (predecessors get time to publish, the value loads fly meanwhile)
 #pragma unroll
   for (int i = 0; i < ITEMS; ++i) {
-    const uint32_t dd = (seg + i * 32 + lane < valid) ? ((uint32_t)(key[i] >> shift) & digit_mask) : (uint32_t)(RADIX - 1);
+    const uint32_t dd = (uint32_t)(key[i] >> shift) & digit_mask;
     const uint32_t slot = s_cta_base[dd] + s_wcnt[warp][dd] + rank[i];
     s_keys[slot] = key[i];
     rank[i] = slot;
@@ -370,16 +368,25 @@ __global__ void __launch_bounds__(SORT_THREADS, 3) sort_onesweep_kernel(const Ke
     const int local = seg + i * 32 + lane;
     val[i] = (local < valid) ? (vals_in ? vals_in[tile_base + local] : (uint32_t)(tile_base + local)) : 0u;
   }
-  // decoupled look-back for digit d
+  // decoupled look-back for digit d, four predecessors per round trip
   uint32_t excl = 0;
   if (tile > 0) {
     int64_t t = (int64_t)tile - 1;
-    while (true) {
-      uint32_t s;
-      do { s = ld_relaxed_u32(lookback + (size_t)t * RADIX + d); } while ((s >> 30) == 0u);
-      excl += s & LB_MASK;
-      if ((s >> 30) == 2u) break;
-      --t;
+    bool found = false;
+    while (!found) {
+      uint32_t w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) w[j] = (t - j >= 0) ? ld_relaxed_u32(lookback + (size_t)(t - j) * RADIX + d) : LB_INC;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (!found) {
+          uint32_t v = w[j];
+          while ((v >> 30) == 0u) v = ld_relaxed_u32(lookback + (size_t)(t - j) * RADIX + d);
+          excl += v & LB_MASK;
+          found = (v >> 30) == 2u;
+        }
+      }
+      t -= 4;
     }
     st_relaxed_u32(my_lb, LB_INC | ((excl + cnt_valid) & LB_MASK));
   }
@@ -431,9 +438,9 @@ cudaError_t launch_scan(GeomView g, int64_t P, cudaStream_t s) {
 cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, uint32_t* tkeys, uint32_t* vals, int64_t capacity,
                              cudaStream_t s) {
   if (a.P <= 0) return cudaSuccess;
-  const int64_t per_block = 256 * DUP_ITEMS;
+  const int64_t per_block = DUP_WARPS * DUP_SEG;
   const unsigned blocks = (unsigned)((a.P + per_block - 1) / per_block);
-  duplicate_kernel<<<blocks, 256, 0, s>>>(g, a.P, a.grid_x, tkeys, vals, capacity);
+  duplicate_kernel<<<blocks, DUP_WARPS * 32, 0, s>>>(g, a.P, a.grid_x, tkeys, vals, capacity);
   return cudaGetLastError();
 }
 

@@ -113,6 +113,29 @@ class ViewParallelRasterizer:
         self.loss_acc = torch.zeros(2, dtype=torch.float32, device=self.device)
         self.last_launches = 0
         self.last_num_rendered: List[int] = []
+        self._copy_stream = None
+
+    def _upload(self, i, targets, priors, masks):
+        items = [targets[i], None if priors is None else priors.get(i), None if masks is None else masks.get(i)]
+        if self.device.type != "cuda" or all(t is None or t.device == self.device for t in items):
+            return items, None
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(self.device)
+        with torch.cuda.stream(self._copy_stream):
+            items = [None if t is None else t.to(self.device, non_blocking=True) for t in items]
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+        return items, ev
+
+    def _await(self, staged):
+        items, ev = staged
+        if ev is not None:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(ev)
+            for t in items:
+                if t is not None:
+                    t.record_stream(cur)
+        return items
 
     @property
     def world(self) -> int:
@@ -136,9 +159,14 @@ class ViewParallelRasterizer:
         self.last_launches = 0
         self.last_num_rendered = []
         outs = []
-        for i in my:
-            r = self.backend(gaussians, views[i], targets[i], None if priors is None else priors.get(i),
-                             None if masks is None else masks.get(i), w_depth, acc, self.loss_acc)
+        # Per-view images (target / prior / mask) may live in pinned HOST memory: they are uploaded on a side
+        # stream one view ahead of the rasterizer, so the host->device copies overlap the kernels.
+        pending = self._upload(my[0], targets, priors, masks) if len(my) else None
+        for k, i in enumerate(my):
+            cur = pending
+            pending = self._upload(my[k + 1], targets, priors, masks) if k + 1 < len(my) else None
+            tgt, pri, msk = self._await(cur)
+            r = self.backend(gaussians, views[i], tgt, pri, msk, w_depth, acc, self.loss_acc)
             self.last_launches += int(r.get("launches", 0))
             self.last_num_rendered.append(int(r.get("num_rendered", 0)))
             if keep_outputs:
