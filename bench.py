@@ -351,7 +351,12 @@ def main():
         "blend_fwd": ("fp32_simt", 15 * work["n_test"] / nv + 11 * work["n_acc"] / nv),
         "bwd_zero": ("hbm", 48 * Pn),
         "blend_bwd": ("fp32_simt", 15 * work["n_test_bwd"] / nv + 59 * work["n_acc"] / nv),
-        "preprocess_bwd": ("hbm", 284 * V + 236 * Pn),
+        # batch path: SH backward deferred -> per view K9 reads radii 4P, params 44V, moments 48V, records 48V, writes the
+        # masked colour gradient 12P and read-modify-writes means/opacity/scales/rotations/densify (52V each way)
+        "preprocess_bwd": ("hbm", 16 * Pn + 244 * V),
+        # once per step: means 12, SH 192, V_local colour gradients 12 each, SH gradient 192 (+192 read when accumulating),
+        # means gradient 24
+        "sh_bwd": ("hbm", Pn * (12 + 192 + 12 * max(work["views"], 1) + 384 + 24)),
         "loss": ("hbm", 36 * HW),
     }
     traffic = {}

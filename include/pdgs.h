@@ -103,6 +103,11 @@ typedef struct PdgsGrads {       /* any pointer may be NULL = not wanted */
   float* densify_grad_accum; /* [P] += || dL/dmeans2D.xy ||  (xyz_gradient_accum) */
   float* densify_denom;      /* [P] += 1                      (denom) */
   int32_t* max_radii2D;      /* [P]  = max(old, radii)        (max_radii2D) */
+  /* Deferred SH backward (batch path).  When non-NULL (SH path only) backward writes this view's clamp-masked
+   * dL/d(rgb) per Gaussian here (zeros for culled ones) and does NOT touch `shs` nor add the view-direction term
+   * to `means3D`: both are produced for all views of a batch at once by pdgs_sh_backward_views(), which reads the
+   * SH coefficients and writes their gradient once per batch instead of once per view. */
+  float* color_grad_view;    /* [P,3] */
 } PdgsGrads;
 
 const char* pdgs_last_error(void);
@@ -119,7 +124,8 @@ int pdgs_destroy(PdgsHandle* h);
 enum {
   PDGS_STAGE_PREPROCESS = 0, PDGS_STAGE_SCAN = 1, PDGS_STAGE_DUPLICATE = 2, PDGS_STAGE_SORT = 3,
   PDGS_STAGE_RANGES = 4, PDGS_STAGE_BLEND_FWD = 5, PDGS_STAGE_BWD_ZERO = 6, PDGS_STAGE_BLEND_BWD = 7,
-  PDGS_STAGE_PREPROCESS_BWD = 8, PDGS_STAGE_LOSS = 9, PDGS_STAGE_DEPTH_SORT = 10, PDGS_STAGE_COUNT = 11
+  PDGS_STAGE_PREPROCESS_BWD = 8, PDGS_STAGE_LOSS = 9, PDGS_STAGE_DEPTH_SORT = 10, PDGS_STAGE_SH_BWD = 11,
+  PDGS_STAGE_COUNT = 12
 };
 int pdgs_set_stage_timing(PdgsHandle* h, int32_t enable);
 int pdgs_stage_times(PdgsHandle* h, float* ms_sum, int32_t* counts, int32_t n);
@@ -142,6 +148,15 @@ int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, P
 int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, const PdgsState* state,
                   const int32_t* radii, int64_t num_rendered, const float* dL_dcolor, const float* dL_dinvdepth,
                   void* scratch, size_t scratch_bytes, const PdgsGrads* grads, void* stream);
+
+/* SH part of the backward for a batch of views (see PdgsGrads.color_grad_view): for every Gaussian and every view v,
+ *   grad_shs[k][c]  (+)= basis_k(dir_v) * color_grads[v][c],   dir_v = normalize(mean - campos_views[v])
+ *   grad_means3D    +=  d(rgb)/d(mean) through dir_v           (the view-direction term of K9)
+ * color_grads: [n_views][P][3] device, campos_views: [n_views][3] device.  accumulate = 0 overwrites grad_shs
+ * (grad_means3D is always added to).  Replaces n_views read-modify-writes of the [P,M,3] SH gradient by one. */
+int pdgs_sh_backward_views(PdgsHandle* h, const PdgsScene* scene, int32_t sh_degree, const float* campos_views,
+                           const float* color_grads, int32_t n_views, float* grad_shs, float* grad_means3D,
+                           int32_t accumulate, void* stream);
 
 /* Image-space loss of one view and its cotangents in one pass (the caller-side torch ops at
  * /root/reference/train.py:153 `l1_loss` = utils/loss_utils.py:40-41 and :174 the depth-prior term):

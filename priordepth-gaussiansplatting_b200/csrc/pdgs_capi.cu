@@ -293,6 +293,7 @@ int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, 
   gp.rotations = grads->rotations; gp.cov3D_precomp = grads->cov3D_precomp; gp.accumulate = grads->accumulate;
   gp.densify_grad_accum = grads->densify_grad_accum; gp.densify_denom = grads->densify_denom;
   gp.max_radii2D = grads->max_radii2D;
+  gp.color_grad_view = a.shs ? grads->color_grad_view : nullptr;
   {
     StageTimer t(h, PDGS_STAGE_PREPROCESS_BWD, s);
     PD_STEP(debug, s, launch_preprocess_backward(a, g, radii, acc, gp, s));
@@ -310,6 +311,25 @@ int pdgs_image_loss(PdgsHandle* h, const float* color, const float* target, cons
   StageTimer t(h, PDGS_STAGE_LOSS, s);
   PD_CUDA(launch_image_loss(color, target, invdepth, prior, mask, width, height, w_color, w_depth, dL_dcolor,
                             dL_dinvdepth, loss, s));
+  return PDGS_OK;
+}
+
+int pdgs_sh_backward_views(PdgsHandle* h, const PdgsScene* scene, int32_t sh_degree, const float* campos_views,
+                           const float* color_grads, int32_t n_views, float* grad_shs, float* grad_means3D,
+                           int32_t accumulate, void* stream) {
+  if (!h || !scene || !campos_views || !color_grads || n_views < 0)
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views: bad argument");
+  if (scene->P <= 0 || n_views == 0) return PDGS_OK;
+  if (!scene->means3D || !scene->shs || scene->M < 1 || scene->M > 16)
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views: means3D / shs missing or M outside 1..16");
+  if (sh_degree < 0 || sh_degree > 3 || (sh_degree + 1) * (sh_degree + 1) > scene->M)
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views: sh_degree needs more coefficients than shs holds");
+  if (scene->M == 16 && (!aligned16(scene->shs) || (grad_shs && !aligned16(grad_shs))))
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views: shs / grad_shs must be 16-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  StageTimer t(h, PDGS_STAGE_SH_BWD, s);
+  PD_CUDA(launch_sh_backward_views(scene->means3D, scene->shs, scene->P, scene->M, sh_degree, campos_views, color_grads,
+                                   n_views, grad_shs, grad_means3D, accumulate, s));
   return PDGS_OK;
 }
 

@@ -199,9 +199,13 @@ struct GradPtrs {
   float* means3D; float* means2D; float* shs; float* colors_precomp; float* opacities; float* scales;
   float* rotations; float* cov3D_precomp; int accumulate;
   float* densify_grad_accum; float* densify_denom; int32_t* max_radii2D;
+  float* color_grad_view;  // deferred SH backward: masked dL/drgb of this view instead of SH / direction gradients
 };
 cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const int32_t* radii, const float* acc,
                                        GradPtrs gp, cudaStream_t s);
+cudaError_t launch_sh_backward_views(const float* means3D, const float* shs, int64_t P, int M, int sh_degree,
+                                     const float* campos_views, const float* color_grads, int n_views, float* grad_shs,
+                                     float* grad_means3D, int accumulate, cudaStream_t s);
 cudaError_t launch_image_loss(const float* color, const float* target, const float* invdepth, const float* prior,
                               const float* mask, int W, int H, float w_color, float w_depth, float* dL_dcolor,
                               float* dL_dinvdepth, float* loss, cudaStream_t s);

@@ -275,12 +275,12 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
 // ------------------------------------------------------------------------------------------
 constexpr int PB_TILE = 256;
 
-struct PbShared {
-  float sh_in[PB_TILE * 48];
-  float sh_out[PB_TILE * 48];
+struct PbShared {  // the deferred-SH variant allocates only the part before sh_in
   float acc_in[PB_TILE * ACC_FLOATS];
   Camera cam;
   unsigned long long bar;
+  float sh_in[PB_TILE * 48];
+  float sh_out[PB_TILE * 48];
 };
 
 struct ShRow {  // SH block of one Gaussian in shared memory
@@ -288,7 +288,10 @@ struct ShRow {  // SH block of one Gaussian in shared memory
   __device__ __forceinline__ float operator()(int i) const { return p[i]; }
 };
 
-__global__ void __launch_bounds__(PB_TILE, 2) preprocess_backward_sh_kernel(DeviceArgs a, GeomView g,
+// DEFER: the SH part of the backward is left to sh_backward_views_kernel (one pass per batch of views); this
+// kernel then only emits the view's masked dL/drgb and never reads or writes an SH row.
+template <bool DEFER>
+__global__ void __launch_bounds__(PB_TILE, DEFER ? 3 : 2) preprocess_backward_sh_kernel(DeviceArgs a, GeomView g,
                                                                            const int32_t* __restrict__ radii,
                                                                            const float* __restrict__ acc, GradPtrs gp,
                                                                            int bulk_ok) {
@@ -308,13 +311,14 @@ __global__ void __launch_bounds__(PB_TILE, 2) preprocess_backward_sh_kernel(Devi
     const bool bulk = bulk_ok && n == PB_TILE;  // full tile and 16-byte aligned arrays
     if (bulk) {
       if (tid == 0) {
-        const uint32_t sh_bytes = (uint32_t)(PB_TILE * row * sizeof(float)), acc_bytes = PB_TILE * ACC_FLOATS * 4;
+        const uint32_t sh_bytes = DEFER ? 0u : (uint32_t)(PB_TILE * row * sizeof(float)), acc_bytes = PB_TILE * ACC_FLOATS * 4;
         mbar_expect_tx(reinterpret_cast<uint64_t*>(&sm.bar), sh_bytes + acc_bytes);
-        bulk_g2s(sm.sh_in, a.shs + (size_t)t0 * row, sh_bytes, reinterpret_cast<uint64_t*>(&sm.bar));
+        if (!DEFER) bulk_g2s(sm.sh_in, a.shs + (size_t)t0 * row, sh_bytes, reinterpret_cast<uint64_t*>(&sm.bar));
         bulk_g2s(sm.acc_in, acc + (size_t)t0 * ACC_FLOATS, acc_bytes, reinterpret_cast<uint64_t*>(&sm.bar));
       }
     } else {
-      for (int i = tid; i < n * row; i += PB_TILE) sm.sh_in[i] = __ldg(a.shs + (size_t)t0 * row + i);
+      if (!DEFER)
+        for (int i = tid; i < n * row; i += PB_TILE) sm.sh_in[i] = __ldg(a.shs + (size_t)t0 * row + i);
       for (int i = tid; i < n * ACC_FLOATS; i += PB_TILE) sm.acc_in[i] = __ldg(acc + (size_t)t0 * ACC_FLOATS + i);
     }
     // per-thread inputs that are small or already coalesced come straight from global memory
@@ -338,16 +342,20 @@ __global__ void __launch_bounds__(PB_TILE, 2) preprocess_backward_sh_kernel(Devi
       opacity = __ldg(a.opacities + idx);
       gA = g.gA[idx]; gB = g.gB[idx]; gC = g.gC[idx];
     }
-    if (tid == 0) bulk_wait_read0();  // the previous tile's bulk store has finished reading sh_out
+    if (!DEFER && tid == 0) bulk_wait_read0();  // the previous tile's bulk store has finished reading sh_out
     __syncthreads();
     if (bulk) {
       mbar_wait(reinterpret_cast<uint64_t*>(&sm.bar), phase);
       phase ^= 1u;
     }
-    float* out_row = sm.sh_out + tid * row;
+    float* out_row = DEFER ? nullptr : sm.sh_out + tid * row;
+    const bool want_sh = !DEFER && gp.shs != nullptr;
     if (!vis) {
-      if (gp.shs) {
+      if (want_sh) {
         for (int k = 0; k < row; ++k) out_row[k] = 0.f;
+      }
+      if (DEFER && in_range) {
+        gp.color_grad_view[3 * idx] = 0.f; gp.color_grad_view[3 * idx + 1] = 0.f; gp.color_grad_view[3 * idx + 2] = 0.f;
       }
       if (in_range && !gp.accumulate) {  // dense zero rows for culled Gaussians
         if (gp.means3D) { gp.means3D[3 * idx] = 0.f; gp.means3D[3 * idx + 1] = 0.f; gp.means3D[3 * idx + 2] = 0.f; }
@@ -382,38 +390,42 @@ __global__ void __launch_bounds__(PB_TILE, 2) preprocess_backward_sh_kernel(Devi
       float grgb[3];
 #pragma unroll
       for (int c = 0; c < 3; ++c) grgb[c] = ((in.clamped >> c) & 1u) ? 0.f : in.g_rgb[c];
-      const float dx = mx - cam.campos[0], dy = my - cam.campos[1], dz = mz - cam.campos[2];
-      float gdir[3], basis[16];
-      if (M == 16) {
-        ShRegs sh;
-        const float4* src = reinterpret_cast<const float4*>(sm.sh_in + tid * 48);
-#pragma unroll
-        for (int k = 0; k < 12; ++k) {
-          const float4 v = src[k];
-          sh.v[4 * k] = v.x; sh.v[4 * k + 1] = v.y; sh.v[4 * k + 2] = v.z; sh.v[4 * k + 3] = v.w;
-        }
-        sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
+      if (DEFER) {
+        gp.color_grad_view[3 * idx] = grgb[0]; gp.color_grad_view[3 * idx + 1] = grgb[1]; gp.color_grad_view[3 * idx + 2] = grgb[2];
       } else {
-        ShRow sh{sm.sh_in + tid * row};
-        sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
-      }
-      g_mean[0] += gdir[0]; g_mean[1] += gdir[1]; g_mean[2] += gdir[2];
-      if (gp.shs) {
-        const int ncoef = sh_num_coeffs(cam.sh_degree);
+        const float dx = mx - cam.campos[0], dy = my - cam.campos[1], dz = mz - cam.campos[2];
+        float gdir[3], basis[16];
         if (M == 16) {
-          float out[48];
+          ShRegs sh;
+          const float4* src = reinterpret_cast<const float4*>(sm.sh_in + tid * 48);
 #pragma unroll
-          for (int k = 0; k < 16; ++k) {
-            const float bk = (k < ncoef) ? basis[k] : 0.f;
-            out[3 * k] = bk * grgb[0]; out[3 * k + 1] = bk * grgb[1]; out[3 * k + 2] = bk * grgb[2];
+          for (int k = 0; k < 12; ++k) {
+            const float4 v = src[k];
+            sh.v[4 * k] = v.x; sh.v[4 * k + 1] = v.y; sh.v[4 * k + 2] = v.z; sh.v[4 * k + 3] = v.w;
           }
-          float4* dst = reinterpret_cast<float4*>(out_row);
-#pragma unroll
-          for (int k = 0; k < 12; ++k) dst[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+          sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
         } else {
-          for (int k = 0; k < M; ++k) {
-            const float bk = (k < ncoef) ? basis[k] : 0.f;
-            out_row[3 * k] = bk * grgb[0]; out_row[3 * k + 1] = bk * grgb[1]; out_row[3 * k + 2] = bk * grgb[2];
+          ShRow sh{sm.sh_in + tid * row};
+          sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
+        }
+        g_mean[0] += gdir[0]; g_mean[1] += gdir[1]; g_mean[2] += gdir[2];
+        if (want_sh) {
+          const int ncoef = sh_num_coeffs(cam.sh_degree);
+          if (M == 16) {
+            float out[48];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+              const float bk = (k < ncoef) ? basis[k] : 0.f;
+              out[3 * k] = bk * grgb[0]; out[3 * k + 1] = bk * grgb[1]; out[3 * k + 2] = bk * grgb[2];
+            }
+            float4* dst = reinterpret_cast<float4*>(out_row);
+#pragma unroll
+            for (int k = 0; k < 12; ++k) dst[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+          } else {
+            for (int k = 0; k < M; ++k) {
+              const float bk = (k < ncoef) ? basis[k] : 0.f;
+              out_row[3 * k] = bk * grgb[0]; out_row[3 * k + 1] = bk * grgb[1]; out_row[3 * k + 2] = bk * grgb[2];
+            }
           }
         }
       }
@@ -460,7 +472,7 @@ __global__ void __launch_bounds__(PB_TILE, 2) preprocess_backward_sh_kernel(Devi
       if (gp.densify_denom) gp.densify_denom[idx] += 1.0f;
       if (gp.max_radii2D) gp.max_radii2D[idx] = max(gp.max_radii2D[idx], radius);
     }
-    if (gp.shs) {
+    if (want_sh) {
       fence_async_smem();  // generic-proxy writes of sh_out -> visible to the bulk store
       __syncthreads();
       float* dst = gp.shs + (size_t)t0 * row;
@@ -479,7 +491,93 @@ __global__ void __launch_bounds__(PB_TILE, 2) preprocess_backward_sh_kernel(Devi
       __syncthreads();  // sh_in / acc_in are free for the next tile's copies
     }
   }
-  if (tid == 0) bulk_wait0();  // all bulk stores complete before the CTA's shared memory goes away
+  if (!DEFER && tid == 0) bulk_wait0();  // all bulk stores complete before the CTA's shared memory goes away
+}
+
+// ------------------------------------------------------------------------------------------
+// SH backward of a whole batch of views (deferred from K9, see PdgsGrads.color_grad_view).
+// One thread per Gaussian: the 3M SH coefficients are read ONCE and their gradient written ONCE per batch;
+// per view only the 12-byte masked dL/drgb is read.  For each view that touched the Gaussian the thread
+// rebuilds the basis for that camera's view direction, adds basis_k * dL/drgb_c to its 3M register
+// accumulators and the direction term to dL/dmean.
+// ------------------------------------------------------------------------------------------
+constexpr int SHV_THREADS = 128;
+constexpr int SHV_MAX_VIEWS = 256;  // camera positions staged per launch (longer batches loop on the host)
+
+template <int MT>  // MT = 16: fully unrolled register path; MT = 0: any M through global memory
+__global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_kernel(const float* __restrict__ means3D,
+                                                                        const float* __restrict__ shs, int64_t P, int M,
+                                                                        int sh_degree,
+                                                                        const float* __restrict__ campos_views,
+                                                                        const float* __restrict__ color_grads,
+                                                                        int n_views, float* __restrict__ grad_shs,
+                                                                        float* __restrict__ grad_means3D, int accumulate) {
+  __shared__ float s_cam[SHV_MAX_VIEWS * 3];
+  for (int i = threadIdx.x; i < n_views * 3; i += SHV_THREADS) s_cam[i] = __ldg(campos_views + i);
+  __syncthreads();
+  const int64_t idx = (int64_t)blockIdx.x * SHV_THREADS + threadIdx.x;
+  if (idx >= P) return;
+  const float mx = __ldg(means3D + 3 * idx), my = __ldg(means3D + 3 * idx + 1), mz = __ldg(means3D + 3 * idx + 2);
+  const int ncoef = sh_num_coeffs(sh_degree);
+  float gm[3] = {0.f, 0.f, 0.f};
+  if (MT == 16) {
+    ShRegs sh;
+    const float4* src = reinterpret_cast<const float4*>(shs + (size_t)idx * 48);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+      const float4 v = __ldg(src + k);
+      sh.v[4 * k] = v.x; sh.v[4 * k + 1] = v.y; sh.v[4 * k + 2] = v.z; sh.v[4 * k + 3] = v.w;
+    }
+    float acc[48];
+#pragma unroll
+    for (int k = 0; k < 48; ++k) acc[k] = 0.f;
+    bool any = false;
+    for (int v = 0; v < n_views; ++v) {
+      const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
+      const float g[3] = {__ldg(gsrc), __ldg(gsrc + 1), __ldg(gsrc + 2)};
+      if (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f) continue;  // culled in this view, or no gradient reached it
+      any = true;
+      float gdir[3], basis[16];
+      sh_backward_dir(sh_degree, mx - s_cam[3 * v], my - s_cam[3 * v + 1], mz - s_cam[3 * v + 2], sh, g, gdir, basis);
+      gm[0] += gdir[0]; gm[1] += gdir[1]; gm[2] += gdir[2];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const float bk = (k < ncoef) ? basis[k] : 0.f;
+        acc[3 * k] = fmaf(bk, g[0], acc[3 * k]);
+        acc[3 * k + 1] = fmaf(bk, g[1], acc[3 * k + 1]);
+        acc[3 * k + 2] = fmaf(bk, g[2], acc[3 * k + 2]);
+      }
+    }
+    if (grad_shs && (any || !accumulate)) {
+      float4* dst = reinterpret_cast<float4*>(grad_shs + (size_t)idx * 48);
+#pragma unroll
+      for (int k = 0; k < 12; ++k) {
+        float4 o = make_float4(acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
+        if (accumulate) { const float4 w = dst[k]; o.x += w.x; o.y += w.y; o.z += w.z; o.w += w.w; }
+        dst[k] = o;
+      }
+    }
+  } else {
+    ShGlobal sh{shs + (size_t)idx * M * 3};
+    float* dst = grad_shs ? grad_shs + (size_t)idx * M * 3 : nullptr;
+    if (dst && !accumulate)
+      for (int k = 0; k < 3 * M; ++k) dst[k] = 0.f;
+    for (int v = 0; v < n_views; ++v) {
+      const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
+      const float g[3] = {__ldg(gsrc), __ldg(gsrc + 1), __ldg(gsrc + 2)};
+      if (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f) continue;
+      float gdir[3], basis[16];
+      sh_backward_dir(sh_degree, mx - s_cam[3 * v], my - s_cam[3 * v + 1], mz - s_cam[3 * v + 2], sh, g, gdir, basis);
+      gm[0] += gdir[0]; gm[1] += gdir[1]; gm[2] += gdir[2];
+      if (dst)
+        for (int k = 0; k < ncoef; ++k) {
+          dst[3 * k] += basis[k] * g[0]; dst[3 * k + 1] += basis[k] * g[1]; dst[3 * k + 2] += basis[k] * g[2];
+        }
+    }
+  }
+  if (grad_means3D && (gm[0] != 0.f || gm[1] != 0.f || gm[2] != 0.f)) {
+    grad_means3D[3 * idx] += gm[0]; grad_means3D[3 * idx + 1] += gm[1]; grad_means3D[3 * idx + 2] += gm[2];
+  }
 }
 
 __global__ void mark_visible_kernel(const float* __restrict__ means3D, const float* __restrict__ viewmatrix, int64_t P,
@@ -511,21 +609,48 @@ cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const in
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     if (dev < 0 || dev >= 64 || !configured[dev]) {
-      e = cudaFuncSetAttribute(preprocess_backward_sh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      e = cudaFuncSetAttribute(preprocess_backward_sh_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                (int)sizeof(PbShared));
       if (e != cudaSuccess) return e;
       if (dev >= 0 && dev < 64) configured[dev] = true;
     }
     const auto al16 = [](const void* p) { return (((uintptr_t)p) & 15u) == 0; };
-    const int bulk_ok = al16(a.shs) && al16(acc) && (!gp.shs || al16(gp.shs));
     const int64_t ntiles = (a.P + PB_TILE - 1) / PB_TILE;
+    if (gp.color_grad_view) {  // SH backward deferred to launch_sh_backward_views: only the accumulator block is staged
+      const int bulk_ok = al16(acc);
+      const unsigned blocks = (unsigned)(ntiles < 3 * 148 ? ntiles : 3 * 148);
+      preprocess_backward_sh_kernel<true><<<blocks, PB_TILE, offsetof(PbShared, sh_in), s>>>(a, g, radii, acc, gp, bulk_ok);
+      return cudaGetLastError();
+    }
+    const int bulk_ok = al16(a.shs) && al16(acc) && (!gp.shs || al16(gp.shs));
     const unsigned blocks = (unsigned)(ntiles < 2 * 148 ? ntiles : 2 * 148);  // persistent: two CTAs per SM
-    preprocess_backward_sh_kernel<<<blocks, PB_TILE, sizeof(PbShared), s>>>(a, g, radii, acc, gp, bulk_ok);
+    preprocess_backward_sh_kernel<false><<<blocks, PB_TILE, sizeof(PbShared), s>>>(a, g, radii, acc, gp, bulk_ok);
     return cudaGetLastError();
   }
   const unsigned blocks = (unsigned)((a.P + PRE_THREADS - 1) / PRE_THREADS);
   preprocess_backward_kernel<<<blocks, PRE_THREADS, 0, s>>>(a, g, radii, acc, gp);
   return cudaGetLastError();
+}
+
+cudaError_t launch_sh_backward_views(const float* means3D, const float* shs, int64_t P, int M, int sh_degree,
+                                     const float* campos_views, const float* color_grads, int n_views, float* grad_shs,
+                                     float* grad_means3D, int accumulate, cudaStream_t s) {
+  if (P <= 0 || n_views <= 0) return cudaSuccess;
+  const unsigned blocks = (unsigned)((P + SHV_THREADS - 1) / SHV_THREADS);
+  for (int v0 = 0; v0 < n_views; v0 += SHV_MAX_VIEWS) {  // later chunks always add to what the first one wrote
+    const int nv = (n_views - v0 < SHV_MAX_VIEWS) ? n_views - v0 : SHV_MAX_VIEWS;
+    const int acc = (v0 == 0) ? accumulate : 1;
+    const float* cg = color_grads + (size_t)v0 * P * 3;
+    if (M == 16)
+      sh_backward_views_kernel<16><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs, P, M, sh_degree, campos_views + 3 * v0, cg,
+                                                                  nv, grad_shs, grad_means3D, acc);
+    else
+      sh_backward_views_kernel<0><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs, P, M, sh_degree, campos_views + 3 * v0, cg,
+                                                                 nv, grad_shs, grad_means3D, acc);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 cudaError_t launch_mark_visible(const float* means3D, const float* viewmatrix, int64_t P, uint8_t* present,

@@ -117,7 +117,10 @@ __device__ __forceinline__ void stage_entry(Stage& st, bool valid, uint32_t src,
   st.mask[threadIdx.x] = (uint8_t)m;
 }
 
-__global__ void __launch_bounds__(RT, 4) render_forward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
+#ifndef PDGS_FWD_CTAS
+#define PDGS_FWD_CTAS 5
+#endif
+__global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
                                                             const float4* __restrict__ gC,
                                                             const uint2* __restrict__ ranges,
                                                             const uint32_t* __restrict__ point_list, int W, int H,

@@ -46,7 +46,7 @@ class PdgsForwardOut(C.Structure):
 class PdgsGrads(C.Structure):
     _fields_ = [("means3D", vp), ("means2D", vp), ("shs", vp), ("colors_precomp", vp), ("opacities", vp),
                 ("scales", vp), ("rotations", vp), ("cov3D_precomp", vp), ("accumulate", C.c_int32),
-                ("densify_grad_accum", vp), ("densify_denom", vp), ("max_radii2D", vp)]
+                ("densify_grad_accum", vp), ("densify_denom", vp), ("max_radii2D", vp), ("color_grad_view", vp)]
 
 
 class PdgsStateView(C.Structure):
@@ -71,6 +71,7 @@ SYMBOLS = {
                                C.POINTER(PdgsForwardOut), C.c_int32, C.POINTER(C.c_int64), vp]),
     "pdgs_backward": (C.c_int, [vp, C.POINTER(PdgsScene), C.POINTER(PdgsCamera), C.POINTER(PdgsState), vp,
                                 C.c_int64, vp, vp, vp, C.c_size_t, C.POINTER(PdgsGrads), vp]),
+    "pdgs_sh_backward_views": (C.c_int, [vp, C.POINTER(PdgsScene), C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int32, vp]),
     "pdgs_mark_visible": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp]),
     "pdgs_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "pdgs_sort_pairs": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int32, vp, C.c_size_t, vp]),
@@ -78,7 +79,7 @@ SYMBOLS = {
 }
 
 STAGES = ("preprocess", "scan", "duplicate", "sort", "ranges", "blend_fwd", "bwd_zero", "blend_bwd", "preprocess_bwd", "loss",
-          "depth_sort")
+          "depth_sort", "sh_bwd")
 
 _lib = None
 _lock = threading.Lock()

@@ -21,6 +21,7 @@ _capacity_hint = {}
 # number of kernels of ours launched by the last forward / backward (for bench.py's gpu_launches)
 LAUNCHES_FORWARD = 0
 LAUNCHES_BACKWARD = 0
+LAUNCHES_SH_BWD = 0
 LAUNCHES_LOSS = 0
 
 
@@ -215,6 +216,8 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
             g.densify_grad_accum = _ptr(accumulate_into.get("densify_grad_accum"))
             g.densify_denom = _ptr(accumulate_into.get("densify_denom"))
             g.max_radii2D = _ptr(accumulate_into.get("max_radii2D"))
+            # deferred SH backward (sh_backward_views): this view only leaves its masked dL/drgb [P,3]
+            g.color_grad_view = _ptr(accumulate_into.get("color_grad_view")) if sh is not None else None
         if P > 0:
             scratch = torch.empty(lib.pdgs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
             cam = _camera(bg, scale_modifier, viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh_degree, campos,
@@ -226,6 +229,31 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
                                       C.byref(g), stream), "pdgs_backward")
             LAUNCHES_BACKWARD = 2 if num_rendered > 0 else 1
     return dmeans2D, dcolors, dopac, dmeans3D, dcov, dsh, dscales, drots
+
+
+def sh_backward_views(means3D, sh, sh_degree, campos_views, color_grads, grad_shs, grad_means3D, accumulate=True):
+    """SH part of the backward for a batch of views at once (C ABI pdgs_sh_backward_views): reads `color_grads`
+    [V,P,3] (what backward left in accumulate_into["color_grad_view"] per view) and `campos_views` [V,3]; writes
+    or accumulates grad_shs [P,M,3] and adds the view-direction term to grad_means3D [P,3]."""
+    global LAUNCHES_SH_BWD
+    lib = L.lib()
+    dev = means3D.device
+    if not means3D.is_cuda:
+        raise L.PdgsError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
+    means3D, sh = _f32c(means3D, "means3D", dev), _f32c(sh, "sh", dev)
+    campos_views, color_grads = _f32c(campos_views, "campos_views", dev), _f32c(color_grads, "color_grads", dev)
+    P, M, V = means3D.shape[0], sh.shape[1], int(campos_views.shape[0])
+    if color_grads.numel() != V * P * 3:
+        raise L.PdgsError("color_grads must be [V,P,3]")
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        sc = _scene(P, means3D, sh, None, None, None, None, None)
+        L.check(lib.pdgs_sh_backward_views(h, C.byref(sc), int(sh_degree), _ptr(campos_views), _ptr(color_grads), V,
+                                           _ptr(grad_shs), _ptr(grad_means3D), int(bool(accumulate)), stream),
+                "pdgs_sh_backward_views")
+        LAUNCHES_SH_BWD = (V + 255) // 256
+    return grad_shs, grad_means3D
 
 
 def image_loss(color, target, invdepth=None, prior=None, mask=None, w_color=1.0, w_depth=0.0, loss_acc=None):

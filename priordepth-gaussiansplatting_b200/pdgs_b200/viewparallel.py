@@ -114,6 +114,7 @@ class ViewParallelRasterizer:
         self.last_launches = 0
         self.last_num_rendered: List[int] = []
         self._copy_stream = None
+        self._color_grads = None
 
     def _upload(self, i, targets, priors, masks):
         items = [targets[i], None if priors is None else priors.get(i), None if masks is None else masks.get(i)]
@@ -159,6 +160,13 @@ class ViewParallelRasterizer:
         self.last_launches = 0
         self.last_num_rendered = []
         outs = []
+        # Deferred SH backward (CUDA backend, SH colours): every view leaves only its masked dL/drgb [P,3]; the SH
+        # coefficients are read and their gradient written once per batch by pdgs_sh_backward_views.
+        defer = self.backend is _cuda_view_backend and gaussians.get("shs") is not None and len(my) > 0
+        if defer:
+            need = (len(my), self.buf.P, 3)
+            if self._color_grads is None or tuple(self._color_grads.shape) != need:
+                self._color_grads = torch.empty(need, dtype=torch.float32, device=self.device)
         # Per-view images (target / prior / mask) may live in pinned HOST memory: they are uploaded on a side
         # stream one view ahead of the rasterizer, so the host->device copies overlap the kernels.
         pending = self._upload(my[0], targets, priors, masks) if len(my) else None
@@ -166,11 +174,19 @@ class ViewParallelRasterizer:
             cur = pending
             pending = self._upload(my[k + 1], targets, priors, masks) if k + 1 < len(my) else None
             tgt, pri, msk = self._await(cur)
+            if defer:
+                acc["color_grad_view"] = self._color_grads[k]
             r = self.backend(gaussians, views[i], tgt, pri, msk, w_depth, acc, self.loss_acc)
             self.last_launches += int(r.get("launches", 0))
             self.last_num_rendered.append(int(r.get("num_rendered", 0)))
             if keep_outputs:
                 outs.append(r)
+        if defer:
+            from . import rasterizer as rz
+            campos = torch.stack([views[i].campos.reshape(3) for i in my]).to(self.device, torch.float32)
+            rz.sh_backward_views(gaussians["means3D"], gaussians["shs"], views[my[0]].sh_degree, campos,
+                                 self._color_grads, acc["shs"], acc["means3D"], accumulate=True)
+            self.last_launches += rz.LAUNCHES_SH_BWD
         if reduce and self.world > 1:
             self.buf.all_reduce(self.group)
             dist.all_reduce(self.loss_acc, op=dist.ReduceOp.SUM, group=self.group)
