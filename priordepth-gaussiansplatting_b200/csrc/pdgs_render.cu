@@ -195,6 +195,34 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// Explicit 32-bit shared-memory addressing for the backward hot loop.  Through C++ references the compiler
+// rebuilt the CTA's shared window base (S2R SR_CgaCtaId + LEA) on every list entry (ncu r01t: 3 instructions and
+// the longest stall of the loop); an opaque base register plus ld/st.shared with immediate offsets avoids that.
+__device__ __forceinline__ uint32_t smem_base(const void* p) {
+  uint32_t a = (uint32_t)__cvta_generic_to_shared(p), r;
+  asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(a));
+  return r;
+}
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ float2 lds64(uint32_t a) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts64(uint32_t a, float x, float y) {
+  asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t x) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(x) : "memory"); }
+
 constexpr int FB = 16;  // Gaussians per phase-2 panel
 
 struct WarpPanel {
@@ -204,23 +232,28 @@ struct WarpPanel {
   uint32_t pos[FB];   // its position in point_list
 };
 
+constexpr uint32_t WP_GPIX = (uint32_t)offsetof(WarpPanel, gpix), WP_GXY = (uint32_t)offsetof(WarpPanel, gxy),
+                   WP_POS = (uint32_t)offsetof(WarpPanel, pos);
+constexpr uint32_t ST_B = (uint32_t)offsetof(Stage, b), ST_C = (uint32_t)offsetof(Stage, c);
+
 // Phase 2: reduce `count` panel rows to per-Gaussian sums and add them to the global accumulator.
-__device__ __forceinline__ void flush_panel(WarpPanel& wp, int count, int lane, float X0f, float Y0f,
+// wp = shared-memory address of the warp's panel.
+__device__ __forceinline__ void flush_panel(uint32_t wp, int count, int lane, float X0f, float Y0f,
                                             const uint32_t* __restrict__ point_list, float* __restrict__ acc) {
   __syncwarp();
   const int g = lane & (FB - 1), half = lane >> 4;
   uint32_t id = 0;
-  if (half == 0 && g < count) id = __ldg(point_list + wp.pos[g]);  // staged a moment ago: an L1/L2 hit, used last
+  if (half == 0 && g < count) id = __ldg(point_list + lds32(wp + WP_POS + 4 * g));  // staged a moment ago: an L1/L2 hit
   float Sz = 0.f, Szx = 0.f, Szy = 0.f, Szxx = 0.f, Szxy = 0.f, Szyy = 0.f, Sw0 = 0.f, Sw1 = 0.f, Sw2 = 0.f, Swd = 0.f;
   if (g < count) {
-    const float2 gxy = wp.gxy[g];
+    const float2 gxy = lds64(wp + WP_GXY + 8 * g);
     const float bx = gxy.x - X0f;                        // dx of pixel column 0 of the patch
     const float by = (gxy.y - Y0f) - (float)(2 * half);  // dy of the first pixel row of this half
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       const int p = half * 16 + i;
-      const float2 zw = wp.zw[g][p ^ g];
-      const float4 gp = wp.gpix[p];
+      const float2 zw = lds64(wp + 8 * (g * 32 + (p ^ g)));
+      const float4 gp = lds128(wp + WP_GPIX + 16 * p);
       const float dx = bx - (float)(i & 7), dy = by - (float)(i >> 3);
       const float zdx = zw.x * dx, zdy = zw.x * dy;
       Sz += zw.x;
@@ -269,7 +302,7 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
   __shared__ uint32_t s_max[NWARP];
   static_assert(sizeof(Stage) + NWARP * sizeof(WarpPanel) + NWARP * 4 <= 48 * 1024, "static shared memory budget");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  WarpPanel& wp = panels[warp];
+  const uint32_t wp = smem_base(&panels[warp]), sst = smem_base(&st);
   const int X0 = blockIdx.x * TILE + (warp & 1) * 8, Y0 = blockIdx.y * TILE + (warp >> 1) * 4;
   const int px = X0 + (lane & 7), py = Y0 + (lane >> 3);
   const bool inside = px < W && py < H;
@@ -286,7 +319,7 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
     gp2 = dL_dcolor[2 * hw + pix];
     if (dL_dinvdepth) gpd = dL_dinvdepth[pix];
   }
-  wp.gpix[lane] = make_float4(gp0, gp1, gp2, gpd);
+  panels[warp].gpix[lane] = make_float4(gp0, gp1, gp2, gpd);
   // -T_final * (bg . dL/dC): the background term of dL/dalpha is this times 1/(1-alpha)
   const float bg_term = -T_final * (__ldg(bg + 0) * gp0 + __ldg(bg + 1) * gp1 + __ldg(bg + 2) * gp2);
   // the tile only needs list positions below the largest n_contrib of its pixels, each warp below its own
@@ -320,8 +353,8 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
         mw &= mw - 1;
         const uint32_t pos = top - (uint32_t)j;
         if (pos >= wmax) continue;
-        const float4 a = st.a[j];
-        const float4 b = st.b[j];
+        const float4 a = lds128(sst + 16 * j);
+        const float4 b = lds128(sst + ST_B + 16 * j);
         const float dx = a.x - pxf, dy = a.y - pyf;
         const float power = gauss_power(dx, dy, a.z, a.w, b.x);
         const float G = gauss_G(power);
@@ -330,7 +363,7 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
         if (!__any_sync(FULL, active)) continue;
         float z = 0.f, w = 0.f;
         if (active) {
-          const float2 c = st.c[j];
+          const float2 c = lds64(sst + ST_C + 8 * j);
           const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
           T *= inv;
           w = alpha * T;
@@ -347,10 +380,10 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
           dL_dalpha = fmaf(dL_dalpha, T, bg_term * inv);
           z = G * dL_dalpha;
         }
-        wp.zw[slot][lane ^ slot] = make_float2(z, w);
+        sts64(wp + 8 * (slot * 32 + (lane ^ slot)), z, w);
         if (lane == 0) {
-          wp.gxy[slot] = make_float2(a.x, a.y);
-          wp.pos[slot] = range.x + pos;
+          sts64(wp + WP_GXY + 8 * slot, a.x, a.y);
+          sts32(wp + WP_POS + 4 * slot, range.x + pos);
         }
         if (++slot == FB) {
           flush_panel(wp, FB, lane, X0f, Y0f, point_list, acc);
