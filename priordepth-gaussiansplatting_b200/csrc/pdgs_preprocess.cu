@@ -132,15 +132,15 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
   const float4 gA = g.gA[idx], gB = g.gB[idx], gC = g.gC[idx];
   BwdIn in;
   {
-    // acc holds the raw pixel moments of z = G*dL/dalpha about the Gaussian's centre (pdgs_render.cu):
+    // acc holds the raw pixel moments of z = o*G*dL/dalpha about the Gaussian's centre (pdgs_render.cu):
     //   a0 = (sum z dx, sum z dy, sum z dx^2, sum z dx dy), a1 = (sum z dy^2, sum z, sum w dL/dD, -), a2 = sum w dL/dC
-    // with d = centre - pixel.  dL/dG = o*dL/dalpha, dG/dd = -G (A dx + B dy, C dy + B dx), dG/dconic = -0.5 G d d^T.
+    // with d = centre - pixel.  dL/dG = o*dL/dalpha, dG/dd = -G (A dx + B dy, C dy + B dx), dG/dconic = -0.5 G d d^T,
+    // dL/do = sum G dL/dalpha = (sum z) / o.
     const float cA = gA.z, cB = gA.w, cC = gB.x, o = gB.y;
-    in.g_mean2d_x = -o * (0.5f * (float)a.W) * (cA * a0.x + cB * a0.y);
-    in.g_mean2d_y = -o * (0.5f * (float)a.H) * (cC * a0.y + cB * a0.x);
-    const float ho = -0.5f * o;
-    in.g_conic_x = ho * a0.z; in.g_conic_y = ho * a0.w; in.g_conic_w = ho * a1.x;
-    in.g_opacity = a1.y; in.g_invdepth = a1.z;
+    in.g_mean2d_x = -(0.5f * (float)a.W) * (cA * a0.x + cB * a0.y);
+    in.g_mean2d_y = -(0.5f * (float)a.H) * (cC * a0.y + cB * a0.x);
+    in.g_conic_x = -0.5f * a0.z; in.g_conic_y = -0.5f * a0.w; in.g_conic_w = -0.5f * a1.x;
+    in.g_opacity = (o > 0.f) ? a1.y / o : 0.f; in.g_invdepth = a1.z;
     in.g_rgb[0] = a2.x; in.g_rgb[1] = a2.y; in.g_rgb[2] = a2.z;
   }
   in.clamped = __float_as_uint(gC.w);
@@ -373,13 +373,12 @@ __global__ void __launch_bounds__(PB_TILE, DEFER ? 3 : 2) preprocess_backward_sh
       const float4 a0 = accv[0], a1 = accv[1], a2 = accv[2];
       BwdIn in;
       {
-        // acc holds the raw pixel moments of z = G*dL/dalpha about the Gaussian's centre (pdgs_render.cu)
+        // acc holds the raw pixel moments of z = o*G*dL/dalpha about the Gaussian's centre (pdgs_render.cu)
         const float cA = gA.z, cB = gA.w, cC = gB.x, o = gB.y;
-        in.g_mean2d_x = -o * (0.5f * (float)a.W) * (cA * a0.x + cB * a0.y);
-        in.g_mean2d_y = -o * (0.5f * (float)a.H) * (cC * a0.y + cB * a0.x);
-        const float ho = -0.5f * o;
-        in.g_conic_x = ho * a0.z; in.g_conic_y = ho * a0.w; in.g_conic_w = ho * a1.x;
-        in.g_opacity = a1.y; in.g_invdepth = a1.z;
+        in.g_mean2d_x = -(0.5f * (float)a.W) * (cA * a0.x + cB * a0.y);
+        in.g_mean2d_y = -(0.5f * (float)a.H) * (cC * a0.y + cB * a0.x);
+        in.g_conic_x = -0.5f * a0.z; in.g_conic_y = -0.5f * a0.w; in.g_conic_w = -0.5f * a1.x;
+        in.g_opacity = (o > 0.f) ? a1.y / o : 0.f; in.g_invdepth = a1.z;
         in.g_rgb[0] = a2.x; in.g_rgb[1] = a2.y; in.g_rgb[2] = a2.z;
       }
       in.clamped = __float_as_uint(gC.w);

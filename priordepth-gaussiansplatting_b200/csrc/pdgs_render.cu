@@ -39,10 +39,12 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
-// power = -0.5*(A dx^2 + C dy^2) - B dx dy, fixed order (hA = -0.5A, hC = -0.5C, nB = -B are exact)
-__device__ __forceinline__ float gauss_power(float dx, float dy, float hA, float nB, float hC) {
+// Exponent of alpha in base 2: t = log2(o) + log2(e) * (-0.5*(A dx^2 + C dy^2) - B dx dy), fixed order.  The staged
+// coefficients are pre-scaled (hA = -0.5 A log2e, nB = -B log2e, hC = -0.5 C log2e, L = log2 o), so
+// alpha = ex2(t) costs no multiply by log2(e) or by the opacity, and "power > 0" is "t > L".
+__device__ __forceinline__ float gauss_exponent(float dx, float dy, float hA, float nB, float hC, float L) {
   const float u = __fmaf_rn(hA, dx, __fmul_rn(nB, dy));
-  const float v = __fmul_rn(__fmul_rn(hC, dy), dy);
+  const float v = __fmaf_rn(__fmul_rn(hC, dy), dy, L);
   return __fmaf_rn(dx, u, v);
 }
 __device__ __forceinline__ float rcp_approx(float x) {
@@ -50,18 +52,18 @@ __device__ __forceinline__ float rcp_approx(float x) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-__device__ __forceinline__ float gauss_G(float power) { return ex2_approx(__fmul_rn(power, LOG2E)); }
 
 // Mask of the warp patches (bit = warp index = row*2 + col; 2 columns of 8 px, 4 rows of 4 px) of the
 // tile at (tx0, ty0) that the alpha >= 1/255 footprint of a Gaussian can reach.  Conservative: the
 // threshold carries a margin far above the fp32 error of the per-pixel evaluation, and any
 // non-finite / non-positive-definite input keeps every patch.
-__device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, float B, float C, float o, float tx0,
-                                               float ty0) {
+__device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, float B, float C, float o, float log2o,
+                                               float tx0, float ty0) {
   const float o255 = 255.0f * o;
   if (!(o255 >= 0.999f)) return (o255 == o255) ? 0u : 0xFFu;  // alpha < 1/255 everywhere
   if (!(A > 0.f) || !(C > 0.f)) return 0xFFu;
-  const float tau = fmaf(__logf(o255), 1.002f, 0.02f);
+  // ln(255 o) = (log2 o + log2 255) ln 2, with the margin
+  const float tau = fmaf((log2o + 7.994353436858858f) * 0.6931471805599453f, 1.002f, 0.02f);
   const float hA = 0.5f * A, hC = 0.5f * C;
   const float sx = -B * __fdividef(1.0f, A);  // argmin over dx on a row dy = const:  dx* = sx * dy
   const float sy = -B * __fdividef(1.0f, C);  // argmin over dy on a column dx = const
@@ -95,8 +97,8 @@ __device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, floa
 }
 
 struct Stage {          // 41 bytes per staged list entry
-  float4 a[RT];         // x, y, -0.5*conA, -conB
-  float4 b[RT];         // -0.5*conC, opacity, 1/depth, r
+  float4 a[RT];         // x, y, -0.5*conA*log2e, -conB*log2e
+  float4 b[RT];         // -0.5*conC*log2e, log2(opacity), 1/depth, r
   float2 c[RT];         // g, b
   uint8_t mask[RT];     // warp patches the Gaussian can reach
 };
@@ -109,10 +111,11 @@ __device__ __forceinline__ void stage_entry(Stage& st, bool valid, uint32_t src,
   if (valid) {
     const uint32_t id = __ldg(point_list + src);
     const float4 a = __ldg(gA + id), b = __ldg(gB + id), c = __ldg(gC + id);
-    st.a[threadIdx.x] = make_float4(a.x, a.y, -0.5f * a.z, -a.w);
-    st.b[threadIdx.x] = make_float4(-0.5f * b.x, b.y, b.z, c.x);
+    const float L = __log2f(b.y);
+    st.a[threadIdx.x] = make_float4(a.x, a.y, (-0.5f * LOG2E) * a.z, -LOG2E * a.w);
+    st.b[threadIdx.x] = make_float4((-0.5f * LOG2E) * b.x, L, b.z, c.x);
     st.c[threadIdx.x] = make_float2(c.y, c.z);
-    m = patch_mask(a.x, a.y, a.z, a.w, b.x, b.y, tx0, ty0);
+    m = patch_mask(a.x, a.y, a.z, a.w, b.x, b.y, L, tx0, ty0);
   }
   st.mask[threadIdx.x] = (uint8_t)m;
 }
@@ -149,16 +152,18 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
     const int cnt = min((uint32_t)RT, range.y - base);
     const uint32_t pos0 = base - range.x;
     for (int k = 0; k * 32 < cnt; ++k) {
-      uint32_t mw = __ballot_sync(FULL, (st.mask[k * 32 + lane] & wbit) != 0);
-      while (mw) {
-        const int j = k * 32 + __ffs(mw) - 1;
-        mw &= mw - 1;
+      // survivors of this warp's patch, bit-reversed so that the leading one is the first list entry
+      uint32_t rm = __brev(__ballot_sync(FULL, (st.mask[k * 32 + lane] & wbit) != 0));
+      while (rm) {
+        const int lz = __clz(rm);
+        const int j = k * 32 + lz;
+        rm &= ~(0x80000000u >> lz);
         const float4 a = st.a[j];
         const float4 b = st.b[j];
         const float dx = a.x - pxf, dy = a.y - pyf;
-        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-        const float alpha = fminf(ALPHA_MAX, __fmul_rn(b.y, gauss_G(power)));
-        if (done || power > 0.0f || alpha < ALPHA_MIN) continue;
+        const float t = gauss_exponent(dx, dy, a.z, a.w, b.x, b.y);
+        const float alpha = fminf(ALPHA_MAX, ex2_approx(t));
+        if (done || t > b.y || alpha < ALPHA_MIN) continue;
         const float test_T = T * (1.0f - alpha);
         if (test_T < T_EPS) {
           done = true;
@@ -225,48 +230,62 @@ __device__ __forceinline__ void sts32(uint32_t a, uint32_t x) { asm volatile("st
 
 constexpr int FB = 16;  // Gaussians per phase-2 panel
 
-struct WarpPanel {
-  float2 zw[FB][32];  // (z, w) of (Gaussian slot g, pixel lane p) at column p ^ g: conflict-free for lane = p and lane = g
-  float4 gpix[32];    // dL/dC rgb, dL/dD of the warp's pixels
-  float2 gxy[FB];     // centre of the slot's Gaussian
-  uint32_t pos[FB];   // its position in point_list
-};
-
-constexpr uint32_t WP_GPIX = (uint32_t)offsetof(WarpPanel, gpix), WP_GXY = (uint32_t)offsetof(WarpPanel, gxy),
-                   WP_POS = (uint32_t)offsetof(WarpPanel, pos);
+// Per-warp panel in dynamic shared memory (byte offsets from the warp's base):
+//   FB rows of PROW bytes: [0, 256) (z, w) of the warp's 32 pixels, [256, 264) centre of the row's Gaussian,
+//   [264, 268) its position in point_list; then 32 x float4 (dL/dC rgb, dL/dD) of the warp's pixels.
+// PROW = 280 makes both access patterns conflict-free: lane = pixel writes 8-byte columns of one row, lane = row
+// reads one column (row stride 70 words: 6 g mod 32 is distinct and even for g = 0..15).
+constexpr uint32_t PROW = 280, PR_GXY = 256, PR_POS = 264;
+constexpr uint32_t WP_GPIX = FB * PROW, WP_BYTES = WP_GPIX + 32 * 16;
 constexpr uint32_t ST_B = (uint32_t)offsetof(Stage, b), ST_C = (uint32_t)offsetof(Stage, c);
+constexpr uint32_t BWD_PANELS = (uint32_t)((sizeof(Stage) + 15) / 16 * 16), BWD_SMAX = BWD_PANELS + NWARP * WP_BYTES,
+                   BWD_SMEM = BWD_SMAX + NWARP * 4;
+static_assert(PROW % 8 == 0 && WP_BYTES % 16 == 0, "panel alignment");
 
 // Phase 2: reduce `count` panel rows to per-Gaussian sums and add them to the global accumulator.
-// wp = shared-memory address of the warp's panel.
+// wp = shared-memory address of the warp's panel.  Lane = (row g, pixel half); each lane takes raw moments of
+// z over its 16 pixels about the patch origin (the pixel offsets are compile-time constants, so a pixel costs
+// 1 + 2 [+ 2] FMAs instead of ten operations), then shifts them to the Gaussian's centre once.
 __device__ __forceinline__ void flush_panel(uint32_t wp, int count, int lane, float X0f, float Y0f,
                                             const uint32_t* __restrict__ point_list, float* __restrict__ acc) {
   __syncwarp();
   const int g = lane & (FB - 1), half = lane >> 4;
+  const uint32_t row = wp + PROW * g;
   uint32_t id = 0;
-  if (half == 0 && g < count) id = __ldg(point_list + lds32(wp + WP_POS + 4 * g));  // staged a moment ago: an L1/L2 hit
+  if (half == 0 && g < count) id = __ldg(point_list + lds32(row + PR_POS));  // staged a moment ago: an L1/L2 hit
   float Sz = 0.f, Szx = 0.f, Szy = 0.f, Szxx = 0.f, Szxy = 0.f, Szyy = 0.f, Sw0 = 0.f, Sw1 = 0.f, Sw2 = 0.f, Swd = 0.f;
   if (g < count) {
-    const float2 gxy = lds64(wp + WP_GXY + 8 * g);
-    const float bx = gxy.x - X0f;                        // dx of pixel column 0 of the patch
-    const float by = (gxy.y - Y0f) - (float)(2 * half);  // dy of the first pixel row of this half
+    float m0 = 0.f, mx = 0.f, mxx = 0.f, my = 0.f, mxy = 0.f;  // raw moments: x = 0..7, y = 0..1 (y^2 = y)
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       const int p = half * 16 + i;
-      const float2 zw = lds64(wp + 8 * (g * 32 + (p ^ g)));
+      const float2 zw = lds64(row + 8 * p);
       const float4 gp = lds128(wp + WP_GPIX + 16 * p);
-      const float dx = bx - (float)(i & 7), dy = by - (float)(i >> 3);
-      const float zdx = zw.x * dx, zdy = zw.x * dy;
-      Sz += zw.x;
-      Szx += zdx;
-      Szy += zdy;
-      Szxx = fmaf(zdx, dx, Szxx);
-      Szxy = fmaf(zdx, dy, Szxy);
-      Szyy = fmaf(zdy, dy, Szyy);
+      const float x = (float)(i & 7);
+      m0 += zw.x;
+      if ((i & 7) != 0) {
+        mx = fmaf(zw.x, x, mx);
+        mxx = fmaf(zw.x, x * x, mxx);
+      }
+      if (i >= 8) {
+        my += zw.x;
+        if ((i & 7) != 0) mxy = fmaf(zw.x, x, mxy);
+      }
       Sw0 = fmaf(zw.y, gp.x, Sw0);
       Sw1 = fmaf(zw.y, gp.y, Sw1);
       Sw2 = fmaf(zw.y, gp.z, Sw2);
       Swd = fmaf(zw.y, gp.w, Swd);
     }
+    // d = centre - pixel = (bx - x, by - y)
+    const float2 gxy = lds64(row + PR_GXY);
+    const float bx = gxy.x - X0f;
+    const float by = (gxy.y - Y0f) - (float)(2 * half);
+    Sz = m0;
+    Szx = fmaf(bx, m0, -mx);
+    Szy = fmaf(by, m0, -my);
+    Szxx = fmaf(bx, fmaf(bx, m0, -2.f * mx), mxx);
+    Szyy = fmaf(by, fmaf(by, m0, -2.f * my), my);
+    Szxy = fmaf(bx, Szy, fmaf(-by, mx, mxy));
   }
   Sz += __shfl_xor_sync(FULL, Sz, 16);
   Szx += __shfl_xor_sync(FULL, Szx, 16);
@@ -297,12 +316,11 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
                                                                 const float* __restrict__ dL_dcolor,
                                                                 const float* __restrict__ dL_dinvdepth,
                                                                 float* __restrict__ acc) {
-  __shared__ Stage st;
-  __shared__ WarpPanel panels[NWARP];
-  __shared__ uint32_t s_max[NWARP];
-  static_assert(sizeof(Stage) + NWARP * sizeof(WarpPanel) + NWARP * 4 <= 48 * 1024, "static shared memory budget");
+  extern __shared__ __align__(16) unsigned char bwd_smem[];
+  Stage& st = *reinterpret_cast<Stage*>(bwd_smem);
+  uint32_t* s_max = reinterpret_cast<uint32_t*>(bwd_smem + BWD_SMAX);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t wp = smem_base(&panels[warp]), sst = smem_base(&st);
+  const uint32_t sst = smem_base(bwd_smem), wp = sst + BWD_PANELS + WP_BYTES * warp;
   const int X0 = blockIdx.x * TILE + (warp & 1) * 8, Y0 = blockIdx.y * TILE + (warp >> 1) * 4;
   const int px = X0 + (lane & 7), py = Y0 + (lane >> 3);
   const bool inside = px < W && py < H;
@@ -319,9 +337,9 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
     gp2 = dL_dcolor[2 * hw + pix];
     if (dL_dinvdepth) gpd = dL_dinvdepth[pix];
   }
-  panels[warp].gpix[lane] = make_float4(gp0, gp1, gp2, gpd);
-  // -T_final * (bg . dL/dC): the background term of dL/dalpha is this times 1/(1-alpha)
-  const float bg_term = -T_final * (__ldg(bg + 0) * gp0 + __ldg(bg + 1) * gp1 + __ldg(bg + 2) * gp2);
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(wp + WP_GPIX + 16 * lane), "f"(gp0), "f"(gp1), "f"(gp2),
+               "f"(gpd)
+               : "memory");
   // the tile only needs list positions below the largest n_contrib of its pixels, each warp below its own
   const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
   if (lane == 0) s_max[warp] = wmax;
@@ -333,10 +351,14 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
   const uint32_t wbit = 1u << warp;
   const float X0f = (float)X0, Y0f = (float)Y0;
 
+  // Back to front.  With q_i = c_i . dL/dC + (1/z_i) dL/dD and w_i = alpha_i T_i, the reference's recurrence
+  //   dL/dalpha_i = T_i (c_i - accum_rec_i) . dL/dC - T_final/(1 - alpha_i) (bg . dL/dC)
+  // equals T_i q_i + (bgterm - sum_{j behind i} w_j q_j) / (1 - alpha_i), so the state carried from one entry to
+  // the next is T and ONE scalar `behind` (four FMAs per pair instead of the per-channel accum_rec updates).
   float T = T_final;
-  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ard = 0.f;  // accum_rec
-  float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f, last_alpha = 0.f;
+  float behind = -T_final * (__ldg(bg + 0) * gp0 + __ldg(bg + 1) * gp1 + __ldg(bg + 2) * gp2);
   int slot = 0;
+  uint32_t wrow = wp;  // shared address of the panel row being filled
 
   for (uint32_t done = 0; done < todo; done += RT) {
     __syncthreads();
@@ -345,21 +367,27 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
     __syncthreads();
     const int cnt = min((uint32_t)RT, todo - done);
     const uint32_t top = todo - 1 - done;  // list position of staged entry 0 (entries go back to front)
-    if (top - (uint32_t)(cnt - 1) >= wmax) continue;  // even the deepest staged entry is behind this warp's last one
+    // staged entry j sits at list position top - j; this warp needs positions < wmax only, i.e. j >= jmin
+    const int jmin = (int)top - (int)wmax + 1;
+    if (jmin >= cnt) continue;
     for (int k = 0; k * 32 < cnt; ++k) {
       uint32_t mw = __ballot_sync(FULL, (st.mask[k * 32 + lane] & wbit) != 0);
-      while (mw) {
-        const int j = k * 32 + __ffs(mw) - 1;
-        mw &= mw - 1;
-        const uint32_t pos = top - (uint32_t)j;
-        if (pos >= wmax) continue;
+      const int lo = jmin - k * 32;
+      if (lo >= 32) continue;
+      if (lo > 0) mw &= 0xffffffffu << lo;
+      uint32_t rm = __brev(mw);  // leading one = first entry to visit
+      while (rm) {
+        const int lz = __clz(rm);
+        const int j = k * 32 + lz;
+        rm &= ~(0x80000000u >> lz);
         const float4 a = lds128(sst + 16 * j);
         const float4 b = lds128(sst + ST_B + 16 * j);
         const float dx = a.x - pxf, dy = a.y - pyf;
-        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-        const float G = gauss_G(power);
-        const float alpha = fminf(ALPHA_MAX, __fmul_rn(b.y, G));
-        const bool active = (pos < last_contributor) && !(power > 0.0f) && !(alpha < ALPHA_MIN);
+        const float t = gauss_exponent(dx, dy, a.z, a.w, b.x, b.y);
+        const float araw = ex2_approx(t);  // o * G
+        const float alpha = fminf(ALPHA_MAX, araw);
+        const uint32_t pos = top - (uint32_t)j;
+        const bool active = (pos < last_contributor) && !(t > b.y) && !(alpha < ALPHA_MIN);
         if (!__any_sync(FULL, active)) continue;
         float z = 0.f, w = 0.f;
         if (active) {
@@ -367,27 +395,22 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
           const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
           T *= inv;
           w = alpha * T;
-          const float om = 1.f - last_alpha;
-          ar0 = fmaf(last_alpha, lc0, om * ar0); lc0 = b.w;
-          ar1 = fmaf(last_alpha, lc1, om * ar1); lc1 = c.x;
-          ar2 = fmaf(last_alpha, lc2, om * ar2); lc2 = c.y;
-          ard = fmaf(last_alpha, ld, om * ard); ld = b.z;
-          last_alpha = alpha;
-          float dL_dalpha = (b.w - ar0) * gp0;
-          dL_dalpha = fmaf(c.x - ar1, gp1, dL_dalpha);
-          dL_dalpha = fmaf(c.y - ar2, gp2, dL_dalpha);
-          dL_dalpha = fmaf(b.z - ard, gpd, dL_dalpha);
-          dL_dalpha = fmaf(dL_dalpha, T, bg_term * inv);
-          z = G * dL_dalpha;
+          float q = b.w * gp0;
+          q = fmaf(c.x, gp1, q);
+          q = fmaf(c.y, gp2, q);
+          q = fmaf(b.z, gpd, q);
+          const float dL_dalpha = fmaf(T, q, behind * inv);
+          behind = fmaf(-w, q, behind);
+          z = araw * dL_dalpha;  // = o * G * dL/dalpha; K8/K9 takes the factor o into account
         }
-        sts64(wp + 8 * (slot * 32 + (lane ^ slot)), z, w);
-        if (lane == 0) {
-          sts64(wp + WP_GXY + 8 * slot, a.x, a.y);
-          sts32(wp + WP_POS + 4 * slot, range.x + pos);
-        }
+        sts64(wrow + 8 * lane, z, w);
+        sts64(wrow + PR_GXY, a.x, a.y);  // every lane stores the same words: no lane predicate, no conflict
+        sts32(wrow + PR_POS, range.x + pos);
+        wrow += PROW;
         if (++slot == FB) {
           flush_panel(wp, FB, lane, X0f, Y0f, point_list, acc);
           slot = 0;
+          wrow = wp;
         }
       }
     }
@@ -410,9 +433,19 @@ cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im,
 cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
                                    const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
   if (a.W <= 0 || a.H <= 0) return cudaSuccess;
+  // 49.3 KB of dynamic shared memory per CTA (above the 48 KB static limit): opt in once per device
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (configured_device != dev) {
+    e = cudaFuncSetAttribute(render_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM);
+    if (e != cudaSuccess) return e;
+    configured_device = dev;
+  }
   dim3 grid(a.grid_x, a.grid_y);
-  render_backward_kernel<<<grid, RT, 0, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, a.W, a.H, a.bg,
-                                                             im.final_T, im.n_contrib, dL_dcolor, dL_dinvdepth, acc);
+  render_backward_kernel<<<grid, RT, BWD_SMEM, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, a.W, a.H, a.bg,
+                                                    im.final_T, im.n_contrib, dL_dcolor, dL_dinvdepth, acc);
   return cudaGetLastError();
 }
 
