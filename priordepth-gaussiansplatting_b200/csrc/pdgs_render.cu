@@ -13,15 +13,22 @@
 //    culled Gaussian would have been rejected by every pixel of the patch, so images, n_contrib
 //    and gradients are unchanged; list positions stay those of the un-culled list.
 //  * Backward in two phases per warp.  Phase 1 (lane = pixel) walks the survivors back to front
-//    and, per (pixel, Gaussian), produces just two scalars: w = alpha*T and z = G*dL/dalpha.  They
-//    go to a per-warp [16 Gaussians][32 pixels] shared-memory panel (XOR-swizzled columns).  Phase 2 (lane = Gaussian x
-//    pixel half) turns a full panel into ten per-Gaussian sums -- the moments sum z, z dx, z dy,
-//    z dx^2, z dx dy, z dy^2 about the Gaussian's own centre and sum w*dL/dC_c, sum w*dL/dD -- with
-//    plain FMAs and ONE shuffle step, then issues three red.global.add.v4.f32.  The moments are
+//    and, per (pixel, Gaussian), produces just two scalars: w = alpha*T and z = o*G*dL/dalpha.  The
+//    state carried between entries is T and one scalar (sum of w_j q_j of the entries behind), not
+//    the reference's per-channel accum_rec.  (z, w) go to a per-warp [8 Gaussians][32 pixels]
+//    shared-memory panel (rows padded to 280 bytes: conflict-free for lane = pixel and lane = row).
+//    Phase 2 (lane = Gaussian x pixel row of the patch) turns a full panel into ten per-Gaussian
+//    sums -- the moments sum z, z dx, z dy, z dx^2, z dx dy, z dy^2 about the Gaussian's own centre
+//    (taken raw about the patch origin with compile-time pixel offsets, then shifted once) and
+//    sum w*dL/dC_c, sum w*dL/dD -- then issues three red.global.add.v4.f32.  The moments are
 //    additive over pixels and tiles; the fused preprocess backward (K8+K9) converts them to
 //    dL/dmean2D, dL/dconic, dL/dopacity.  This replaces fifty shuffles per (warp, Gaussian).
-//  * The per-pair alpha is computed by ONE shared function in a fixed operation order so that
-//    forward and backward take bit-identical accept/reject decisions.
+//    Measured on C4 (B200): 8-row panels 0.86 ms vs 16-row panels 1.02 ms (smaller shared footprint
+//    leaves more L1 for the gathers); fetching the next survivor's records early and 5-6 CTAs/SM were
+//    both slower.
+//  * alpha = ex2(log2 o + log2e * power) with the scaled conic and log2 o staged once per entry, by ONE
+//    shared function in a fixed operation order so that forward and backward take bit-identical
+//    accept/reject decisions.
 #include "pdgs_internal.cuh"
 
 namespace pdgs {
@@ -96,10 +103,10 @@ __device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, floa
   return mask;
 }
 
-struct Stage {          // 41 bytes per staged list entry
+struct Stage {          // 49 bytes per staged list entry
   float4 a[RT];         // x, y, -0.5*conA*log2e, -conB*log2e
   float4 b[RT];         // -0.5*conC*log2e, log2(opacity), 1/depth, r
-  float2 c[RT];         // g, b
+  float4 c[RT];         // g, b, Gaussian id (bits), -
   uint8_t mask[RT];     // warp patches the Gaussian can reach
 };
 
@@ -114,7 +121,7 @@ __device__ __forceinline__ void stage_entry(Stage& st, bool valid, uint32_t src,
     const float L = __log2f(b.y);
     st.a[threadIdx.x] = make_float4(a.x, a.y, (-0.5f * LOG2E) * a.z, -LOG2E * a.w);
     st.b[threadIdx.x] = make_float4((-0.5f * LOG2E) * b.x, L, b.z, c.x);
-    st.c[threadIdx.x] = make_float2(c.y, c.z);
+    st.c[threadIdx.x] = make_float4(c.y, c.z, __uint_as_float(id), 0.f);
     m = patch_mask(a.x, a.y, a.z, a.w, b.x, b.y, L, tx0, ty0);
   }
   st.mask[threadIdx.x] = (uint8_t)m;
@@ -170,7 +177,7 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
           tested = pos0 + j + 1;
           continue;
         }
-        const float2 c = st.c[j];
+        const float2 c = make_float2(st.c[j].x, st.c[j].y);
         const float w = alpha * T;
         C0 = fmaf(b.w, w, C0);
         C1 = fmaf(c.x, w, C1);
@@ -228,13 +235,22 @@ __device__ __forceinline__ void sts64(uint32_t a, float x, float y) {
 }
 __device__ __forceinline__ void sts32(uint32_t a, uint32_t x) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(x) : "memory"); }
 
-constexpr int FB = 16;  // Gaussians per phase-2 panel
+#ifndef PDGS_BWD_FB
+#define PDGS_BWD_FB 8
+#endif
+#ifndef PDGS_BWD_CTAS
+#define PDGS_BWD_CTAS 4
+#endif
+constexpr int FB = PDGS_BWD_FB;   // Gaussians per phase-2 panel (8 or 16)
+constexpr int FPARTS = 32 / FB;   // lanes per panel row in phase 2; each covers FB pixels = FB/8 pixel rows of the patch
+static_assert(FB == 8 || FB == 16, "panel rows");
 
 // Per-warp panel in dynamic shared memory (byte offsets from the warp's base):
 //   FB rows of PROW bytes: [0, 256) (z, w) of the warp's 32 pixels, [256, 264) centre of the row's Gaussian,
-//   [264, 268) its position in point_list; then 32 x float4 (dL/dC rgb, dL/dD) of the warp's pixels.
+//   [264, 268) its Gaussian id; then 32 x float4 (dL/dC rgb, dL/dD) of the warp's pixels.
 // PROW = 280 makes both access patterns conflict-free: lane = pixel writes 8-byte columns of one row, lane = row
-// reads one column (row stride 70 words: 6 g mod 32 is distinct and even for g = 0..15).
+// reads one column (row stride 70 words: 6 g mod 32 is distinct and even for g = 0..15; with 8 rows the second
+// lane group of a half-warp sits 16 words further, also distinct).
 constexpr uint32_t PROW = 280, PR_GXY = 256, PR_POS = 264;
 constexpr uint32_t WP_GPIX = FB * PROW, WP_BYTES = WP_GPIX + 32 * 16;
 constexpr uint32_t ST_B = (uint32_t)offsetof(Stage, b), ST_C = (uint32_t)offsetof(Stage, c);
@@ -243,22 +259,22 @@ constexpr uint32_t BWD_PANELS = (uint32_t)((sizeof(Stage) + 15) / 16 * 16), BWD_
 static_assert(PROW % 8 == 0 && WP_BYTES % 16 == 0, "panel alignment");
 
 // Phase 2: reduce `count` panel rows to per-Gaussian sums and add them to the global accumulator.
-// wp = shared-memory address of the warp's panel.  Lane = (row g, pixel half); each lane takes raw moments of
-// z over its 16 pixels about the patch origin (the pixel offsets are compile-time constants, so a pixel costs
+// wp = shared-memory address of the warp's panel.  Lane = (row g, pixel part); each lane takes raw moments of
+// z over its FB pixels about the patch origin (the pixel offsets are compile-time constants, so a pixel costs
 // 1 + 2 [+ 2] FMAs instead of ten operations), then shifts them to the Gaussian's centre once.
 __device__ __forceinline__ void flush_panel(uint32_t wp, int count, int lane, float X0f, float Y0f,
-                                            const uint32_t* __restrict__ point_list, float* __restrict__ acc) {
+                                            float* __restrict__ acc) {
   __syncwarp();
-  const int g = lane & (FB - 1), half = lane >> 4;
+  const int g = lane & (FB - 1), part = lane / FB;
   const uint32_t row = wp + PROW * g;
   uint32_t id = 0;
-  if (half == 0 && g < count) id = __ldg(point_list + lds32(row + PR_POS));  // staged a moment ago: an L1/L2 hit
+  if (part == 0 && g < count) id = lds32(row + PR_POS);
   float Sz = 0.f, Szx = 0.f, Szy = 0.f, Szxx = 0.f, Szxy = 0.f, Szyy = 0.f, Sw0 = 0.f, Sw1 = 0.f, Sw2 = 0.f, Swd = 0.f;
   if (g < count) {
-    float m0 = 0.f, mx = 0.f, mxx = 0.f, my = 0.f, mxy = 0.f;  // raw moments: x = 0..7, y = 0..1 (y^2 = y)
+    float m0 = 0.f, mx = 0.f, mxx = 0.f, my = 0.f, mxy = 0.f;  // raw moments: x = 0..7, y = 0..FB/8-1 (y^2 = y)
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int p = half * 16 + i;
+    for (int i = 0; i < FB; ++i) {
+      const int p = part * FB + i;
       const float2 zw = lds64(row + 8 * p);
       const float4 gp = lds128(wp + WP_GPIX + 16 * p);
       const float x = (float)(i & 7);
@@ -279,7 +295,7 @@ __device__ __forceinline__ void flush_panel(uint32_t wp, int count, int lane, fl
     // d = centre - pixel = (bx - x, by - y)
     const float2 gxy = lds64(row + PR_GXY);
     const float bx = gxy.x - X0f;
-    const float by = (gxy.y - Y0f) - (float)(2 * half);
+    const float by = (gxy.y - Y0f) - (float)((FB / 8) * part);
     Sz = m0;
     Szx = fmaf(bx, m0, -mx);
     Szy = fmaf(by, m0, -my);
@@ -287,17 +303,20 @@ __device__ __forceinline__ void flush_panel(uint32_t wp, int count, int lane, fl
     Szyy = fmaf(by, fmaf(by, m0, -2.f * my), my);
     Szxy = fmaf(bx, Szy, fmaf(-by, mx, mxy));
   }
-  Sz += __shfl_xor_sync(FULL, Sz, 16);
-  Szx += __shfl_xor_sync(FULL, Szx, 16);
-  Szy += __shfl_xor_sync(FULL, Szy, 16);
-  Szxx += __shfl_xor_sync(FULL, Szxx, 16);
-  Szxy += __shfl_xor_sync(FULL, Szxy, 16);
-  Szyy += __shfl_xor_sync(FULL, Szyy, 16);
-  Sw0 += __shfl_xor_sync(FULL, Sw0, 16);
-  Sw1 += __shfl_xor_sync(FULL, Sw1, 16);
-  Sw2 += __shfl_xor_sync(FULL, Sw2, 16);
-  Swd += __shfl_xor_sync(FULL, Swd, 16);
-  if (half == 0 && g < count) {
+#pragma unroll
+  for (int sh = 16; sh >= FB; sh >>= 1) {
+    Sz += __shfl_xor_sync(FULL, Sz, sh);
+    Szx += __shfl_xor_sync(FULL, Szx, sh);
+    Szy += __shfl_xor_sync(FULL, Szy, sh);
+    Szxx += __shfl_xor_sync(FULL, Szxx, sh);
+    Szxy += __shfl_xor_sync(FULL, Szxy, sh);
+    Szyy += __shfl_xor_sync(FULL, Szyy, sh);
+    Sw0 += __shfl_xor_sync(FULL, Sw0, sh);
+    Sw1 += __shfl_xor_sync(FULL, Sw1, sh);
+    Sw2 += __shfl_xor_sync(FULL, Sw2, sh);
+    Swd += __shfl_xor_sync(FULL, Swd, sh);
+  }
+  if (part == 0 && g < count) {
     float* dst = acc + (size_t)id * ACC_FLOATS;
     red_add_v4(dst, Szx, Szy, Szxx, Szxy);
     red_add_v4(dst + 4, Szyy, Sz, Swd, 0.f);
@@ -306,7 +325,7 @@ __device__ __forceinline__ void flush_panel(uint32_t wp, int count, int lane, fl
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
+__global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
                                                                 const float4* __restrict__ gC,
                                                                 const uint2* __restrict__ ranges,
                                                                 const uint32_t* __restrict__ point_list, int W, int H,
@@ -380,42 +399,43 @@ __global__ void __launch_bounds__(RT, 4) render_backward_kernel(const float4* __
         const int lz = __clz(rm);
         const int j = k * 32 + lz;
         rm &= ~(0x80000000u >> lz);
-        const float4 a = lds128(sst + 16 * j);
-        const float4 b = lds128(sst + ST_B + 16 * j);
+        const float4 a = lds128(sst + 16 * j), b = lds128(sst + ST_B + 16 * j);
         const float dx = a.x - pxf, dy = a.y - pyf;
         const float t = gauss_exponent(dx, dy, a.z, a.w, b.x, b.y);
         const float araw = ex2_approx(t);  // o * G
         const float alpha = fminf(ALPHA_MAX, araw);
         const uint32_t pos = top - (uint32_t)j;
         const bool active = (pos < last_contributor) && !(t > b.y) && !(alpha < ALPHA_MIN);
-        if (!__any_sync(FULL, active)) continue;
-        float z = 0.f, w = 0.f;
-        if (active) {
-          const float2 c = lds64(sst + ST_C + 8 * j);
-          const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
-          T *= inv;
-          w = alpha * T;
-          float q = b.w * gp0;
-          q = fmaf(c.x, gp1, q);
-          q = fmaf(c.y, gp2, q);
-          q = fmaf(b.z, gpd, q);
-          const float dL_dalpha = fmaf(T, q, behind * inv);
-          behind = fmaf(-w, q, behind);
-          z = araw * dL_dalpha;  // = o * G * dL/dalpha; K8/K9 takes the factor o into account
-        }
-        sts64(wrow + 8 * lane, z, w);
-        sts64(wrow + PR_GXY, a.x, a.y);  // every lane stores the same words: no lane predicate, no conflict
-        sts32(wrow + PR_POS, range.x + pos);
-        wrow += PROW;
-        if (++slot == FB) {
-          flush_panel(wp, FB, lane, X0f, Y0f, point_list, acc);
-          slot = 0;
-          wrow = wp;
+        if (__any_sync(FULL, active)) {
+          float z = 0.f, w = 0.f;
+          const float4 c = lds128(sst + ST_C + 16 * j);  // uniform address: one broadcast wavefront
+          const uint32_t row_id = __float_as_uint(c.z);
+          if (active) {
+            const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
+            T *= inv;
+            w = alpha * T;
+            float q = b.w * gp0;
+            q = fmaf(c.x, gp1, q);
+            q = fmaf(c.y, gp2, q);
+            q = fmaf(b.z, gpd, q);
+            const float dL_dalpha = fmaf(T, q, behind * inv);
+            behind = fmaf(-w, q, behind);
+            z = araw * dL_dalpha;  // = o * G * dL/dalpha; K8/K9 takes the factor o into account
+          }
+          sts64(wrow + 8 * lane, z, w);
+          sts64(wrow + PR_GXY, a.x, a.y);  // every lane stores the same words: no lane predicate, no conflict
+          sts32(wrow + PR_POS, row_id);
+          wrow += PROW;
+          if (++slot == FB) {
+            flush_panel(wp, FB, lane, X0f, Y0f, acc);
+            slot = 0;
+            wrow = wp;
+          }
         }
       }
     }
   }
-  if (slot > 0) flush_panel(wp, slot, lane, X0f, Y0f, point_list, acc);
+  if (slot > 0) flush_panel(wp, slot, lane, X0f, Y0f, acc);
 }
 
 }  // namespace

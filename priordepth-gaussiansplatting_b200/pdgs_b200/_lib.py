@@ -10,7 +10,8 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "..", "lib", "libpdgs.so")
+# PDGS_LIB: development override used to A/B kernel variants of the same library (never another backend)
+LIB_PATH = os.environ.get("PDGS_LIB") or os.path.join(_HERE, "..", "lib", "libpdgs.so")
 
 PDGS_OK = 0
 PDGS_NEED_BINNING = 1
