@@ -65,7 +65,7 @@ def measured_peaks():
 # --------------------------------------------------------------------------------------------
 # CPU arm: the float64 oracle on a bounded sample (tile window of one view), extrapolated by pairs
 # --------------------------------------------------------------------------------------------
-def oracle_sample(scene, view, window_tiles, threads):
+def oracle_sample(scene, view, window_tiles, threads, return_oracle=False):
     """fwd+bwd of the oracle on the Gaussians touching a centred window of tiles of `view`.
     Returns (seconds, pairs in the window, pairs in the whole view)."""
     import numpy as np
@@ -100,6 +100,8 @@ def oracle_sample(scene, view, window_tiles, threads):
     gc = torch.sign(res.color - target) / target.numel()
     o.backward(gc, None)
     dt = time.perf_counter() - t0
+    if return_oracle:
+        return dt, pairs_window, pairs_view, int(ids.numel()), dict(result=res, window=win, ids=ids)
     return dt, pairs_window, pairs_view, int(ids.numel())
 
 

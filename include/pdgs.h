@@ -169,6 +169,32 @@ int pdgs_image_loss(PdgsHandle* h, const float* color, const float* target, cons
                     const float* prior, const float* mask, int32_t width, int32_t height, float w_color,
                     float w_depth, float* dL_dcolor, float* dL_dinvdepth, float* loss, void* stream);
 
+/* SSIM with the 11x11 Gaussian window (sigma 1.5, zero "same" padding) on planar fp32 images [planes][H][W]; the
+ * map-level interface of the reference's fused-ssim module:
+ *   fusedssim(C1, C2, img1, img2, train) -> (ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12)
+ *       /root/reference/submodules/fused-ssim/ssim.cu:368-404, kernel :187-289, ext.cpp:5
+ *   fusedssim_backward(C1, C2, img1, img2, dL_dmap, dm_dmu1, dm_dsigma1_sq, dm_dsigma12) -> dL_dimg1
+ *       /root/reference/submodules/fused-ssim/ssim.cu:406-444, kernel :291-366, ext.cpp:6
+ * ssim_map may be NULL; the three partial maps are all given (train) or all NULL; ssim_sum (may be NULL) is a DEVICE
+ * accumulator that receives += sum of the map.  dL_dmap NULL = the uniform value dL_dmap_uniform (a mean). */
+int pdgs_ssim_forward(PdgsHandle* h, float C1, float C2, const float* img1, const float* img2, int32_t planes,
+                      int32_t width, int32_t height, float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq,
+                      float* dm_dsigma12, float* ssim_sum, void* stream);
+int pdgs_ssim_backward(PdgsHandle* h, const float* img1, const float* img2, const float* dL_dmap, float dL_dmap_uniform,
+                       const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, int32_t planes,
+                       int32_t width, int32_t height, float* dL_dimg1, void* stream);
+size_t pdgs_ssim_scratch_bytes(int32_t width, int32_t height, int32_t planes);
+
+/* The reference's training loss and its cotangents in three launches (/root/reference/train.py:153-159, 174):
+ *   L = (1 - lambda_dssim) * mean|color - target| + lambda_dssim * (1 - mean ssim(color, target))
+ *       + w_depth * mean|(invdepth - prior) * mask|
+ *   loss[0] += mean L1, loss[1] += mean masked depth L1 (prior != NULL), loss[2] += mean SSIM   (DEVICE float[3])
+ *   dL_dcolor = dL/dcolor, dL_dinvdepth = dL/dinvdepth.  scratch: pdgs_ssim_scratch_bytes(width, height, 3) bytes. */
+int pdgs_image_loss_ssim(PdgsHandle* h, const float* color, const float* target, const float* invdepth,
+                         const float* prior, const float* mask, int32_t width, int32_t height, float lambda_dssim,
+                         float w_depth, void* scratch, size_t scratch_bytes, float* dL_dcolor, float* dL_dinvdepth,
+                         float* loss, void* stream);
+
 int pdgs_mark_visible(const float* means3D, const float* viewmatrix, const float* projmatrix, int64_t P,
                       uint8_t* present, void* stream);
 

@@ -22,6 +22,7 @@ struct StageRec { int stage; cudaEvent_t b, e; };
 struct PdgsHandle {
   int device;
   unsigned long long* host_slot;  // pinned: [0] = num_rendered | overflow << 32
+  double* dsums;                  // device double[8]: loss sums accumulated in double by the SSIM kernels
   cudaEvent_t ev;
   int timing;                     // per-stage events enabled
   std::vector<cudaEvent_t> pool;  // idle timing events
@@ -85,6 +86,7 @@ int pdgs_create(PdgsHandle** out) {
   }
   PD_CUDA(cudaHostAlloc((void**)&h->host_slot, 64, cudaHostAllocDefault));
   PD_CUDA(cudaEventCreateWithFlags(&h->ev, cudaEventDisableTiming));
+  PD_CUDA(cudaMalloc((void**)&h->dsums, 64));
   h->timing = 0;
   *out = h;
   return PDGS_OK;
@@ -93,6 +95,7 @@ int pdgs_create(PdgsHandle** out) {
 int pdgs_destroy(PdgsHandle* h) {
   if (!h) return PDGS_OK;
   cudaFreeHost(h->host_slot);
+  cudaFree(h->dsums);
   cudaEventDestroy(h->ev);
   for (StageRec& r : h->recs) { cudaEventDestroy(r.b); cudaEventDestroy(r.e); }
   for (cudaEvent_t e : h->pool) cudaEventDestroy(e);
@@ -311,6 +314,72 @@ int pdgs_image_loss(PdgsHandle* h, const float* color, const float* target, cons
   StageTimer t(h, PDGS_STAGE_LOSS, s);
   PD_CUDA(launch_image_loss(color, target, invdepth, prior, mask, width, height, w_color, w_depth, dL_dcolor,
                             dL_dinvdepth, loss, s));
+  return PDGS_OK;
+}
+
+size_t pdgs_ssim_scratch_bytes(int32_t width, int32_t height, int32_t planes) {
+  if (width <= 0 || height <= 0 || planes <= 0) return 0;
+  return 3 * align_up((size_t)planes * width * height * sizeof(float));
+}
+
+int pdgs_ssim_forward(PdgsHandle* h, float C1, float C2, const float* img1, const float* img2, int32_t planes,
+                      int32_t width, int32_t height, float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq,
+                      float* dm_dsigma12, float* ssim_sum, void* stream) {
+  if (!h || !img1 || !img2 || planes < 0 || width <= 0 || height <= 0)
+    return fail(PDGS_E_INVALID, "pdgs_ssim_forward: bad argument");
+  const int nd = (dm_dmu1 != nullptr) + (dm_dsigma1_sq != nullptr) + (dm_dsigma12 != nullptr);
+  if (nd != 0 && nd != 3) return fail(PDGS_E_INVALID, "pdgs_ssim_forward: give all three partial maps or none");
+  if (planes > 65535) return fail(PDGS_E_INVALID, "pdgs_ssim_forward: more than 65535 planes");
+  cudaStream_t s = (cudaStream_t)stream;
+  StageTimer t(h, PDGS_STAGE_LOSS, s);
+  if (ssim_sum) PD_CUDA(cudaMemsetAsync(h->dsums, 0, 16, s));
+  PD_CUDA(launch_ssim_forward(C1, C2, img1, img2, planes, width, height, ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12,
+                              ssim_sum ? h->dsums : nullptr, 0, s));
+  if (ssim_sum && planes > 0) PD_CUDA(launch_ssim_finalize(h->dsums, 1.0, ssim_sum, nullptr, s));
+  return PDGS_OK;
+}
+
+int pdgs_ssim_backward(PdgsHandle* h, const float* img1, const float* img2, const float* dL_dmap, float dL_dmap_uniform,
+                       const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, int32_t planes,
+                       int32_t width, int32_t height, float* dL_dimg1, void* stream) {
+  if (!h || !img1 || !img2 || !dm_dmu1 || !dm_dsigma1_sq || !dm_dsigma12 || !dL_dimg1 || planes < 0 || width <= 0 ||
+      height <= 0)
+    return fail(PDGS_E_INVALID, "pdgs_ssim_backward: bad argument");
+  if (planes > 65535) return fail(PDGS_E_INVALID, "pdgs_ssim_backward: more than 65535 planes");
+  cudaStream_t s = (cudaStream_t)stream;
+  StageTimer t(h, PDGS_STAGE_LOSS, s);
+  PD_CUDA(launch_ssim_backward(img1, img2, dL_dmap, dL_dmap_uniform, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, planes, width,
+                               height, 0.f, dL_dimg1, nullptr, 0.0, nullptr, nullptr, s));
+  return PDGS_OK;
+}
+
+int pdgs_image_loss_ssim(PdgsHandle* h, const float* color, const float* target, const float* invdepth,
+                         const float* prior, const float* mask, int32_t width, int32_t height, float lambda_dssim,
+                         float w_depth, void* scratch, size_t scratch_bytes, float* dL_dcolor, float* dL_dinvdepth,
+                         float* loss, void* stream) {
+  if (!h || !color || !target || !dL_dcolor || !loss || width <= 0 || height <= 0)
+    return fail(PDGS_E_INVALID, "pdgs_image_loss_ssim: bad argument");
+  if (prior && (!invdepth || !dL_dinvdepth))
+    return fail(PDGS_E_INVALID, "pdgs_image_loss_ssim: prior given without invdepth / dL_dinvdepth");
+  if (!scratch || scratch_bytes < pdgs_ssim_scratch_bytes(width, height, 3))
+    return fail(PDGS_E_INVALID, "pdgs_image_loss_ssim: scratch smaller than pdgs_ssim_scratch_bytes(width, height, 3)");
+  cudaStream_t s = (cudaStream_t)stream;
+  StageTimer t(h, PDGS_STAGE_LOSS, s);
+  const size_t n = (size_t)3 * width * height, seg = align_up(n * sizeof(float));
+  float* d_mu = (float*)scratch;
+  float* d_s1 = (float*)((char*)scratch + seg);
+  float* d_s12 = (float*)((char*)scratch + 2 * seg);
+  const float inv_n = 1.0f / (float)n;
+  // partial maps into the scratch; sum of the SSIM map and sum |color - target| accumulated in double
+  PD_CUDA(cudaMemsetAsync(h->dsums, 0, 16, s));
+  PD_CUDA(launch_ssim_forward(0.01f * 0.01f, 0.03f * 0.03f, color, target, 3, width, height, nullptr, d_mu, d_s1, d_s12,
+                              h->dsums, 1, s));
+  // d/dcolor [(1 - lambda) mean|c - t| + lambda (1 - mean ssim)]; its first block folds the sums into loss[2], loss[0]
+  PD_CUDA(launch_ssim_backward(color, target, nullptr, -lambda_dssim * inv_n, d_mu, d_s1, d_s12, 3, width, height,
+                               (1.0f - lambda_dssim) * inv_n, dL_dcolor, h->dsums, 1.0 / (double)n, loss + 2, loss + 0, s));
+  if (prior)
+    PD_CUDA(launch_image_loss(nullptr, nullptr, invdepth, prior, mask, width, height, 0.f, w_depth, nullptr, dL_dinvdepth,
+                              loss, s));
   return PDGS_OK;
 }
 

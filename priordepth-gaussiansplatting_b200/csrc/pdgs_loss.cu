@@ -88,10 +88,10 @@ __global__ void __launch_bounds__(LOSS_THREADS) image_loss_kernel(const float* _
 cudaError_t launch_image_loss(const float* color, const float* target, const float* invdepth, const float* prior,
                               const float* mask, int W, int H, float w_color, float w_depth, float* dL_dcolor,
                               float* dL_dinvdepth, float* loss, cudaStream_t s) {
-  const size_t n_depth = (size_t)W * H, n_color = 3 * n_depth;
-  const float gc = w_color / (float)n_color, gd = w_depth / (float)n_depth;
+  const size_t n_depth = (size_t)W * H, n_color = color ? 3 * n_depth : 0;  // color == NULL: depth-prior term only
+  const float gc = n_color ? w_color / (float)n_color : 0.f, gd = w_depth / (float)n_depth;
   const int vec_ok = ((((uintptr_t)color) | ((uintptr_t)target) | ((uintptr_t)dL_dcolor)) & 15u) == 0 ? 1 : 0;
-  size_t blocks = (n_color / 4 + LOSS_THREADS - 1) / LOSS_THREADS;
+  size_t blocks = ((n_color ? n_color : n_depth) / 4 + LOSS_THREADS - 1) / LOSS_THREADS;
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
   image_loss_kernel<<<(unsigned)blocks, LOSS_THREADS, 0, s>>>(color, target, invdepth, prior, mask, n_color, n_depth, gc,

@@ -285,6 +285,89 @@ def image_loss(color, target, invdepth=None, prior=None, mask=None, w_color=1.0,
     return dcolor, ddepth, loss_acc
 
 
+def image_loss_ssim(color, target, invdepth=None, prior=None, mask=None, lambda_dssim=0.2, w_depth=0.0, loss_acc=None,
+                    scratch=None):
+    """The reference's training loss and its cotangents (C ABI pdgs_image_loss_ssim; the torch ops at
+    /root/reference/train.py:153-159 `(1-l)*l1 + l*(1-ssim)` and :174 the depth-prior term).
+    -> (dL_dcolor[3,H,W], dL_dinvdepth[1,H,W] or None, loss_acc[3] = mean L1, mean masked depth L1, mean SSIM)."""
+    global LAUNCHES_LOSS
+    lib = L.lib()
+    dev = color.device
+    if not color.is_cuda:
+        raise L.PdgsError("color must be a CUDA tensor (this rasterizer has no CPU path)")
+    H, W = int(color.shape[-2]), int(color.shape[-1])
+    color = _f32c(color, "color", dev)
+    target = _f32c(target, "target", dev)
+    if target is None or target.numel() != color.numel() or color.numel() != 3 * H * W:
+        raise L.PdgsError("color and target must both be [3,H,W]")
+    invdepth, prior, mask = _f32c(invdepth, "invdepth", dev), _f32c(prior, "prior", dev), _f32c(mask, "mask", dev)
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        need = lib.pdgs_ssim_scratch_bytes(W, H, 3)
+        if scratch is None or scratch.numel() < need:
+            scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+        dcolor = torch.empty_like(color)
+        ddepth = torch.empty(1, H, W, dtype=torch.float32, device=dev) if prior is not None else None
+        if loss_acc is None:
+            loss_acc = torch.zeros(3, dtype=torch.float32, device=dev)
+        L.check(lib.pdgs_image_loss_ssim(h, _ptr(color), _ptr(target), _ptr(invdepth), _ptr(prior), _ptr(mask), W, H,
+                                         float(lambda_dssim), float(w_depth), _ptr(scratch), scratch.numel(), _ptr(dcolor),
+                                         _ptr(ddepth), _ptr(loss_acc), stream), "pdgs_image_loss_ssim")
+        LAUNCHES_LOSS = 3 if prior is not None else 2
+    return dcolor, ddepth, loss_acc
+
+
+def ssim_forward(C1, C2, img1, img2, train=True, want_map=True, ssim_sum=None):
+    """fusedssim(C1, C2, img1, img2, train) of the reference's fused-ssim module
+    (/root/reference/submodules/fused-ssim/ssim.cu:368-404): img [B,CH,H,W] fp32 CUDA ->
+    (ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12); the partial maps are empty tensors when not train."""
+    lib = L.lib()
+    if not img1.is_cuda:
+        raise L.PdgsError("img1 must be a CUDA tensor (no CPU path)")
+    dev = img1.device
+    if img1.dim() != 4 or img1.shape != img2.shape:
+        raise L.PdgsError("img1 and img2 must be [B,CH,H,W] tensors of the same shape")
+    img1, img2 = _f32c(img1, "img1", dev), _f32c(img2, "img2", dev)
+    B, CH, H, W = (int(v) for v in img1.shape)
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        smap = torch.empty_like(img1) if want_map else None
+        if train:
+            d1, d2, d3 = torch.empty_like(img1), torch.empty_like(img1), torch.empty_like(img1)
+        else:
+            d1 = d2 = d3 = None
+        if B * CH > 0 and H * W > 0:
+            L.check(lib.pdgs_ssim_forward(h, float(C1), float(C2), _ptr(img1), _ptr(img2), B * CH, W, H, _ptr(smap), _ptr(d1),
+                                          _ptr(d2), _ptr(d3), _ptr(ssim_sum), stream), "pdgs_ssim_forward")
+    e = torch.empty(0, device=dev)
+    return smap, (d1 if train else e), (d2 if train else e), (d3 if train else e)
+
+
+def ssim_backward(C1, C2, img1, img2, dL_dmap, dm_dmu1, dm_dsigma1_sq, dm_dsigma12):
+    """fusedssim_backward of the reference (/root/reference/submodules/fused-ssim/ssim.cu:406-444) -> dL_dimg1.
+    dL_dmap may be a python float (uniform cotangent of a mean)."""
+    lib = L.lib()
+    dev = img1.device
+    img1, img2 = _f32c(img1, "img1", dev), _f32c(img2, "img2", dev)
+    B, CH, H, W = (int(v) for v in img1.shape)
+    uniform = 0.0
+    if isinstance(dL_dmap, (int, float)):
+        uniform, dL_dmap = float(dL_dmap), None
+    else:
+        dL_dmap = _f32c(dL_dmap, "dL_dmap", dev)
+    d1, d2, d3 = _f32c(dm_dmu1, "dm_dmu1", dev), _f32c(dm_dsigma1_sq, "dm_dsigma1_sq", dev), _f32c(dm_dsigma12, "dm_dsigma12", dev)
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        out = torch.empty_like(img1)
+        if B * CH > 0 and H * W > 0:
+            L.check(lib.pdgs_ssim_backward(h, _ptr(img1), _ptr(img2), _ptr(dL_dmap), uniform, _ptr(d1), _ptr(d2), _ptr(d3),
+                                           B * CH, W, H, _ptr(out), stream), "pdgs_ssim_backward")
+    return out
+
+
 def mark_visible(means3D, viewmatrix, projmatrix):
     """-> bool[P]; the near-plane test of the reference's checkFrustum."""
     lib = L.lib()

@@ -105,7 +105,17 @@ def run_config(name, iters, warmup, cpu_window, check_ints=True, cpu=True):
             pass
         a = A()
         a.cpu_window = cpu_window
-        dt, pw, pv, n = bench.oracle_sample(sc, view, cpu_window, os.cpu_count() or 1)
+        dt, pw, pv, n, orc = bench.oracle_sample(sc, view, cpu_window, os.cpu_count() or 1, return_oracle=True)
+        # image / inverse-depth parity inside the window (the oracle blends only the window's tiles)
+        x0, y0, x1, y1 = orc["window"]
+        ys, xs = slice(16 * y0, min(16 * y1, H)), slice(16 * x0, min(16 * x1, W))
+        res = orc["result"]
+        ok = ~res.fragile[ys, xs]
+        dc = (color.detach().double().cpu()[:, ys, xs] - res.color[:, ys, xs]).abs().max(dim=0).values
+        dd = (invd.detach().double().cpu()[0, ys, xs] - res.invdepth[0, ys, xs]).abs()
+        out["parity_window"] = dict(max_abs_color=float(dc[ok].max()), max_abs_invdepth=float(dd[ok].max()),
+                                    invdepth_max=float(res.invdepth.max()), fragile_pixels=int((~ok).sum()),
+                                    pixels=int(ok.numel()))
         out["cpu_oracle"] = dict(window_tiles=cpu_window, sample_s=dt, pairs_window=pw, pairs_view=pv,
                                  est_view_s=dt * pv / max(pw, 1), cores=os.cpu_count(),
                                  note="float64 CPU oracle fwd+bwd on a centred tile window, extrapolated by pairs")
@@ -133,8 +143,8 @@ def main():
         print(json.dumps(r), flush=True)
     if args.json:
         json.dump(rows, open(args.json, "w"), indent=1)
-    print("\n| Config | P / visible / pairs | fwd ms (p10-p90) | bwd ms (p10-p90) | fwd+bwd ms | CPU oracle est. s/view (cores) | ints bit-exact |")
-    print("|---|---|---|---|---|---|---|")
+    print("\n| Config | P / visible / pairs | fwd ms (p10-p90) | bwd ms (p10-p90) | fwd+bwd ms | CPU oracle est. s/view (cores) | max-abs img / invdepth (window) | ints bit-exact |")
+    print("|---|---|---|---|---|---|---|---|")
     for r in rows:
         f, b = r["fwd_ms"], r["bwd_ms"]
         cpu = r.get("cpu_oracle")
@@ -142,6 +152,8 @@ def main():
               f"{f['median']:.3f} ({f['p10']:.3f}-{f['p90']:.3f}) | " +
               (f"{b['median']:.3f} ({b['p10']:.3f}-{b['p90']:.3f}) | {f['median'] + b['median']:.3f} | " if b else "- | - | ") +
               (f"{cpu['est_view_s']:.0f} ({cpu['cores']}) | " if cpu else "- | ") +
+              (f"{r['parity_window']['max_abs_color']:.1e} / {r['parity_window']['max_abs_invdepth']:.1e} | "
+               if "parity_window" in r else "- | ") +
               f"radii {r.get('radii_bit_exact')}, R {r.get('num_rendered_equal', '-')} |")
 
 
