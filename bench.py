@@ -294,7 +294,7 @@ def main():
     e2e = None
     if not args.no_e2e:
         h2d = sum(v.numel() * 4 for v in host.values()) + sum(cam_host[i].numel() * 4 + tgt_host[i].numel() * 4 for i in my)
-        d2h = 8
+        d2h = 12  # the three loss sums
 
         def e2e_step():
             g = {k: v.to(dev, non_blocking=True) for k, v in host.items()}

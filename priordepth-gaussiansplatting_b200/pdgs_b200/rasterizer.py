@@ -318,6 +318,10 @@ def image_loss_ssim(color, target, invdepth=None, prior=None, mask=None, lambda_
     return dcolor, ddepth, loss_acc
 
 
+def ssim_scratch_bytes(width: int, height: int, planes: int = 3) -> int:
+    return int(L.lib().pdgs_ssim_scratch_bytes(int(width), int(height), int(planes)))
+
+
 def ssim_forward(C1, C2, img1, img2, train=True, want_map=True, ssim_sum=None):
     """fusedssim(C1, C2, img1, img2, train) of the reference's fused-ssim module
     (/root/reference/submodules/fused-ssim/ssim.cu:368-404): img [B,CH,H,W] fp32 CUDA ->

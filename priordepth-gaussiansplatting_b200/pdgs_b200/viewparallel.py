@@ -75,8 +75,10 @@ class GradBuffer:
         return sum((3 * self.M if w is None else w) for _, w in _SEGMENTS)
 
 
-def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, mask, w_depth, acc: Dict, loss_acc):
-    """forward -> image loss -> backward (accumulating) of ONE view on the CUDA library."""
+def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, mask, w_depth, acc: Dict, loss_acc,
+                       lambda_dssim: float = 0.0, scratch: Optional[Dict] = None):
+    """forward -> image loss -> backward (accumulating) of ONE view on the CUDA library.  lambda_dssim > 0 selects
+    the reference's training loss (1-l)*L1 + l*(1-SSIM) (/root/reference/train.py:153-159), else plain L1."""
     from . import rasterizer as rz
     empty = torch.empty(0, device=gaussians["means3D"].device)
     shs = gaussians.get("shs")
@@ -88,8 +90,18 @@ def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, ma
         rs.debug)
     launches = rz.LAUNCHES_FORWARD
     use_depth = prior is not None and w_depth != 0.0
-    dcolor, ddepth, _ = rz.image_loss(color, target, invd if use_depth else None, prior if use_depth else None,
-                                      mask if use_depth else None, 1.0, w_depth, loss_acc)
+    if lambda_dssim > 0.0:
+        buf = None if scratch is None else scratch.get("ssim")
+        need = rz.ssim_scratch_bytes(rs.image_width, rs.image_height)
+        if buf is None or buf.numel() < need:
+            buf = torch.empty(need, dtype=torch.uint8, device=color.device)
+            if scratch is not None:
+                scratch["ssim"] = buf
+        dcolor, ddepth, _ = rz.image_loss_ssim(color, target, invd if use_depth else None, prior if use_depth else None,
+                                               mask if use_depth else None, lambda_dssim, w_depth, loss_acc, buf)
+    else:
+        dcolor, ddepth, _ = rz.image_loss(color, target, invd if use_depth else None, prior if use_depth else None,
+                                          mask if use_depth else None, 1.0, w_depth, loss_acc)
     launches += rz.LAUNCHES_LOSS
     rz.rasterize_gaussians_backward(
         rs.bg, gaussians["means3D"], radii, empty if colors is None else colors, gaussians["opacities"],
@@ -110,7 +122,8 @@ class ViewParallelRasterizer:
         if backend is None and self.device.type != "cuda":
             raise RuntimeError("ViewParallelRasterizer: the rasterizer needs a CUDA device (there is no CPU path)")
         self.buf = GradBuffer(P, M, self.device)
-        self.loss_acc = torch.zeros(2, dtype=torch.float32, device=self.device)
+        self.loss_acc = torch.zeros(3, dtype=torch.float32, device=self.device)  # sums over views: L1, depth L1, SSIM
+        self._scratch: Dict = {}
         self.last_launches = 0
         self.last_num_rendered: List[int] = []
         self._copy_stream = None
@@ -148,7 +161,7 @@ class ViewParallelRasterizer:
 
     def step(self, gaussians: Dict[str, torch.Tensor], views: Sequence, targets: Dict[int, torch.Tensor],
              priors: Optional[Dict[int, torch.Tensor]] = None, masks: Optional[Dict[int, torch.Tensor]] = None,
-             w_depth: float = 0.0, reduce: bool = True, keep_outputs: bool = False) -> Dict:
+             w_depth: float = 0.0, reduce: bool = True, keep_outputs: bool = False, lambda_dssim: float = 0.0) -> Dict:
         """gaussians: means3D/shs/opacities/scales/rotations (post-activation, as render() passes them,
         /root/reference/gaussian_renderer/__init__.py:57-112); views: one GaussianRasterizationSettings per
         camera of the WHOLE batch (identical on every rank); targets/priors/masks: dict view index -> tensor
@@ -176,7 +189,11 @@ class ViewParallelRasterizer:
             tgt, pri, msk = self._await(cur)
             if defer:
                 acc["color_grad_view"] = self._color_grads[k]
-            r = self.backend(gaussians, views[i], tgt, pri, msk, w_depth, acc, self.loss_acc)
+            if self.backend is _cuda_view_backend:
+                r = self.backend(gaussians, views[i], tgt, pri, msk, w_depth, acc, self.loss_acc, lambda_dssim,
+                                 self._scratch)
+            else:
+                r = self.backend(gaussians, views[i], tgt, pri, msk, w_depth, acc, self.loss_acc)
             self.last_launches += int(r.get("launches", 0))
             self.last_num_rendered.append(int(r.get("num_rendered", 0)))
             if keep_outputs:

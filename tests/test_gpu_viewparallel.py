@@ -87,3 +87,32 @@ def test_stage_timing_accumulates_without_sync():
     assert st["preprocess"][1] == 3 and st["blend_bwd"][1] == 3 and st["sort"][1] >= 3
     assert all(ms >= 0.0 for ms, _ in st.values()) and st["blend_fwd"][0] > 0.0
     assert rz.stage_times(DEV)["preprocess"][1] == 0
+
+
+def test_batch_step_with_ssim_training_loss_equals_autograd_through_the_dropin_packages():
+    """The reference's training step (train.py:143-184): render -> (1-l)*L1 + l*(1-fused_ssim) + w*depth L1 ->
+    backward, written with the two drop-in packages and torch autograd, equals the fused batch step."""
+    from fused_ssim import fused_ssim
+    from pdgs_b200.viewparallel import ViewParallelRasterizer
+    sc = scenes.make_config("C4", P=6000, n_views=3, scale_image=0.1)
+    H, W = sc.views[0].image_height, sc.views[0].image_width
+    gen = torch.Generator().manual_seed(5)
+    targets = {i: torch.rand(3, H, W, generator=gen).to(DEV) for i in range(3)}
+    priors = {i: torch.rand(1, H, W, generator=gen).to(DEV) for i in range(3)}
+    lam, w_depth = 0.2, 0.5
+    sums, ssim_sum = None, 0.0
+    for i, view in enumerate(sc.views):
+        lv, color, radii, invd = helpers.run_cuda(sc, view, DEV)
+        s = fused_ssim(color.unsqueeze(0), targets[i].unsqueeze(0))
+        l = (1.0 - lam) * (color - targets[i]).abs().mean() + lam * (1.0 - s) + w_depth * (invd - priors[i]).abs().mean()
+        l.backward()
+        ssim_sum += float(s)
+        g = {k: lv[k].grad for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        sums = g if sums is None else {k: sums[k] + g[k] for k in g}
+    vp = ViewParallelRasterizer(sc.P, 16, DEV)
+    gaussians = {k: getattr(sc, k).to(DEV) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    views = [helpers.cuda_settings(sc, v, DEV) for v in sc.views]
+    vp.step(gaussians, views, targets, priors, None, w_depth, lambda_dssim=lam)
+    for k in sums:
+        assert helpers.rel_err(vp.buf.view(k), sums[k].view_as(vp.buf.view(k))) < 5e-5, k
+    assert abs(float(vp.loss_acc[2]) - ssim_sum) < 1e-4
