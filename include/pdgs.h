@@ -70,6 +70,18 @@ typedef struct PdgsScene {
   const float* scales;          /* [P,3] */
   const float* rotations;       /* [P,4] */
   const float* cov3D_precomp;   /* [P,6] */
+  /* Fused activations + split SH.  These let the caller hand over the optimiser's own
+   * parameter tensors, so the per-iteration torch kernels of /root/reference/scene/gaussian_model.py:103-131
+   * (exp / normalize / sigmoid) and the 192 B/Gaussian torch.cat of get_features (:115-119) disappear.
+   *  - shs_dc + shs_rest replace `shs` (the `dc=`, `shs=` pair render() passes when separate_sh is set,
+   *    /root/reference/gaussian_renderer/__init__.py:82-101): features_dc [P,1,3] and features_rest [P,M-1,3];
+   *    M stays the total coefficient count.  Exactly one of shs / (shs_dc, shs_rest) / colors_precomp is given.
+   *  - raw_params = 1: opacities / scales / rotations hold _opacity / _scaling / _rotation BEFORE activation; K1
+   *    applies sigmoid / exp / x / max(|x|, 1e-12) (gaussian_model.py:40-48) and K9 returns gradients w.r.t. the
+   *    raw tensors.  Ignored for cov3D_precomp (opacity is still activated). */
+  const float* shs_dc;          /* [P,1,3] */
+  const float* shs_rest;        /* [P,M-1,3] (may be NULL when M == 1) */
+  int32_t raw_params;
 } PdgsScene;
 
 /* Per-call state, allocated by the caller with the sizes below (the reference's
@@ -108,6 +120,9 @@ typedef struct PdgsGrads {       /* any pointer may be NULL = not wanted */
    * to `means3D`: both are produced for all views of a batch at once by pdgs_sh_backward_views(), which reads the
    * SH coefficients and writes their gradient once per batch instead of once per view. */
   float* color_grad_view;    /* [P,3] */
+  /* Split SH gradients (scene given as shs_dc / shs_rest): replace `shs`. */
+  float* shs_dc;             /* [P,1,3] */
+  float* shs_rest;           /* [P,M-1,3] */
 } PdgsGrads;
 
 const char* pdgs_last_error(void);
@@ -157,6 +172,10 @@ int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, 
 int pdgs_sh_backward_views(PdgsHandle* h, const PdgsScene* scene, int32_t sh_degree, const float* campos_views,
                            const float* color_grads, int32_t n_views, float* grad_shs, float* grad_means3D,
                            int32_t accumulate, void* stream);
+/* Same for a scene given as shs_dc / shs_rest: gradients go to grad_dc [P,1,3] and grad_rest [P,M-1,3]. */
+int pdgs_sh_backward_views_split(PdgsHandle* h, const PdgsScene* scene, int32_t sh_degree, const float* campos_views,
+                                 const float* color_grads, int32_t n_views, float* grad_dc, float* grad_rest,
+                                 float* grad_means3D, int32_t accumulate, void* stream);
 
 /* Image-space loss of one view and its cotangents in one pass (the caller-side torch ops at
  * /root/reference/train.py:153 `l1_loss` = utils/loss_utils.py:40-41 and :174 the depth-prior term):

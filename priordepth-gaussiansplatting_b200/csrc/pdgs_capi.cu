@@ -143,23 +143,30 @@ static int make_args(const PdgsScene* sc, const PdgsCamera* cam, DeviceArgs& a) 
   if (cam->image_width <= 0 || cam->image_height <= 0) return fail(PDGS_E_INVALID, "image size must be positive");
   if (sc->P > 0) {
     if (!sc->means3D || !sc->opacities) return fail(PDGS_E_INVALID, "means3D/opacities is NULL");
-    if ((sc->shs != nullptr) == (sc->colors_precomp != nullptr))
-      return fail(PDGS_E_INVALID, "exactly one of shs / colors_precomp must be given");
+    const bool split = sc->shs_dc != nullptr;
+    if ((int)(sc->shs != nullptr) + (int)split + (int)(sc->colors_precomp != nullptr) != 1)
+      return fail(PDGS_E_INVALID, "exactly one of shs / (shs_dc, shs_rest) / colors_precomp must be given");
+    if (!split && sc->shs_rest) return fail(PDGS_E_INVALID, "shs_rest given without shs_dc");
+    if (split && sc->M > 1 && !sc->shs_rest) return fail(PDGS_E_INVALID, "shs_rest is NULL but M > 1");
+    if (split && (!aligned16(sc->shs_dc) || (sc->shs_rest && !aligned16(sc->shs_rest))))
+      return fail(PDGS_E_INVALID, "shs_dc / shs_rest must be 16-byte aligned");
     const bool sr = sc->scales != nullptr && sc->rotations != nullptr;
     if (sr == (sc->cov3D_precomp != nullptr) || ((sc->scales != nullptr) != (sc->rotations != nullptr)))
       return fail(PDGS_E_INVALID, "exactly one of (scales, rotations) / cov3D_precomp must be given");
-    if (sc->shs && (sc->M < 1 || sc->M > 16)) return fail(PDGS_E_INVALID, "SH coefficient count M must be in 1..16");
-    if (sc->shs && (cam->sh_degree < 0 || cam->sh_degree > 3 || (cam->sh_degree + 1) * (cam->sh_degree + 1) > sc->M))
+    const bool any_sh = sc->shs || split;
+    if (any_sh && (sc->M < 1 || sc->M > 16)) return fail(PDGS_E_INVALID, "SH coefficient count M must be in 1..16");
+    if (any_sh && (cam->sh_degree < 0 || cam->sh_degree > 3 || (cam->sh_degree + 1) * (cam->sh_degree + 1) > sc->M))
       return fail(PDGS_E_INVALID, "sh_degree needs more coefficients than shs holds (or is outside 0..3)");
     if (sc->rotations && !aligned16(sc->rotations)) return fail(PDGS_E_INVALID, "rotations must be 16-byte aligned");
     if (sc->shs && sc->M == 16 && !aligned16(sc->shs)) return fail(PDGS_E_INVALID, "shs must be 16-byte aligned");
   }
   if (!cam->viewmatrix || !cam->projmatrix || !cam->bg) return fail(PDGS_E_INVALID, "viewmatrix/projmatrix/bg is NULL");
-  if (sc->shs && !cam->campos) return fail(PDGS_E_INVALID, "campos is NULL");
+  if ((sc->shs || sc->shs_dc) && !cam->campos) return fail(PDGS_E_INVALID, "campos is NULL");
+  a.shs_dc = sc->shs_dc; a.shs_rest = sc->shs_dc ? sc->shs_rest : nullptr; a.raw = sc->raw_params ? 1 : 0;
   a.means3D = sc->means3D; a.shs = sc->shs; a.colors_precomp = sc->colors_precomp; a.opacities = sc->opacities;
   a.scales = sc->scales; a.rotations = sc->rotations; a.cov3D_precomp = sc->cov3D_precomp;
   a.viewmatrix = cam->viewmatrix; a.projmatrix = cam->projmatrix; a.campos = cam->campos; a.bg = cam->bg;
-  a.P = sc->P; a.M = sc->shs ? sc->M : 0;
+  a.P = sc->P; a.M = (sc->shs || sc->shs_dc) ? sc->M : 0;
   a.tanfovx = cam->tanfovx; a.tanfovy = cam->tanfovy;
   a.W = cam->image_width; a.H = cam->image_height;
   a.focal_x = (float)a.W / (2.0f * cam->tanfovx);
@@ -296,7 +303,11 @@ int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, 
   gp.rotations = grads->rotations; gp.cov3D_precomp = grads->cov3D_precomp; gp.accumulate = grads->accumulate;
   gp.densify_grad_accum = grads->densify_grad_accum; gp.densify_denom = grads->densify_denom;
   gp.max_radii2D = grads->max_radii2D;
-  gp.color_grad_view = a.shs ? grads->color_grad_view : nullptr;
+  gp.color_grad_view = (a.shs || a.shs_dc) ? grads->color_grad_view : nullptr;
+  gp.shs_dc = a.shs_dc ? grads->shs_dc : nullptr; gp.shs_rest = a.shs_dc ? grads->shs_rest : nullptr;
+  if (!a.shs) gp.shs = nullptr;
+  if ((gp.shs_dc && !aligned16(gp.shs_dc)) || (gp.shs_rest && !aligned16(gp.shs_rest)))
+    return fail(PDGS_E_INVALID, "grad shs_dc / shs_rest must be 16-byte aligned");
   {
     StageTimer t(h, PDGS_STAGE_PREPROCESS_BWD, s);
     PD_STEP(debug, s, launch_preprocess_backward(a, g, radii, acc, gp, s));
@@ -397,8 +408,30 @@ int pdgs_sh_backward_views(PdgsHandle* h, const PdgsScene* scene, int32_t sh_deg
     return fail(PDGS_E_INVALID, "pdgs_sh_backward_views: shs / grad_shs must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   StageTimer t(h, PDGS_STAGE_SH_BWD, s);
-  PD_CUDA(launch_sh_backward_views(scene->means3D, scene->shs, scene->P, scene->M, sh_degree, campos_views, color_grads,
-                                   n_views, grad_shs, grad_means3D, accumulate, s));
+  PD_CUDA(launch_sh_backward_views(scene->means3D, scene->shs, nullptr, nullptr, scene->P, scene->M, sh_degree, campos_views,
+                                   color_grads, n_views, grad_shs, nullptr, nullptr, grad_means3D, accumulate, s));
+  return PDGS_OK;
+}
+
+int pdgs_sh_backward_views_split(PdgsHandle* h, const PdgsScene* scene, int32_t sh_degree, const float* campos_views,
+                                 const float* color_grads, int32_t n_views, float* grad_dc, float* grad_rest,
+                                 float* grad_means3D, int32_t accumulate, void* stream) {
+  if (!h || !scene || !campos_views || !color_grads || n_views < 0)
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views_split: bad argument");
+  if (scene->P <= 0 || n_views == 0) return PDGS_OK;
+  if (!scene->means3D || !scene->shs_dc || scene->M < 1 || scene->M > 16 || (scene->M > 1 && !scene->shs_rest))
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views_split: means3D / shs_dc / shs_rest missing or M outside 1..16");
+  if (sh_degree < 0 || sh_degree > 3 || (sh_degree + 1) * (sh_degree + 1) > scene->M)
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views_split: sh_degree needs more coefficients than the scene holds");
+  if ((grad_dc != nullptr) != (grad_rest != nullptr || scene->M == 1) && scene->M > 1)
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views_split: grad_dc and grad_rest must be given together");
+  if (!aligned16(scene->shs_dc) || (scene->shs_rest && !aligned16(scene->shs_rest)) || (grad_dc && !aligned16(grad_dc)) ||
+      (grad_rest && !aligned16(grad_rest)))
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views_split: SH arrays must be 16-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  StageTimer t(h, PDGS_STAGE_SH_BWD, s);
+  PD_CUDA(launch_sh_backward_views(scene->means3D, nullptr, scene->shs_dc, scene->shs_rest, scene->P, scene->M, sh_degree,
+                                   campos_views, color_grads, n_views, nullptr, grad_dc, grad_rest, grad_means3D, accumulate, s));
   return PDGS_OK;
 }
 

@@ -170,6 +170,8 @@ constexpr int ACC_FLOATS = 12;
 struct DeviceArgs {
   const float* means3D; const float* shs; const float* colors_precomp; const float* opacities;
   const float* scales; const float* rotations; const float* cov3D_precomp;
+  const float* shs_dc; const float* shs_rest;  // split SH (features_dc / features_rest) instead of shs
+  int raw;                                     // opacities / scales / rotations are pre-activation parameters
   const float* viewmatrix; const float* projmatrix; const float* campos; const float* bg;
   int64_t P; int M;
   float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
@@ -200,12 +202,16 @@ struct GradPtrs {
   float* rotations; float* cov3D_precomp; int accumulate;
   float* densify_grad_accum; float* densify_denom; int32_t* max_radii2D;
   float* color_grad_view;  // deferred SH backward: masked dL/drgb of this view instead of SH / direction gradients
+  float* shs_dc; float* shs_rest;  // split SH gradients
 };
 cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const int32_t* radii, const float* acc,
                                        GradPtrs gp, cudaStream_t s);
-cudaError_t launch_sh_backward_views(const float* means3D, const float* shs, int64_t P, int M, int sh_degree,
-                                     const float* campos_views, const float* color_grads, int n_views, float* grad_shs,
-                                     float* grad_means3D, int accumulate, cudaStream_t s);
+// shs != NULL: packed [P,M,3] rows, gradient to grad_shs.  Otherwise split rows (shs_dc [P,3], shs_rest [P,3(M-1)]),
+// gradients to grad_dc / grad_rest.
+cudaError_t launch_sh_backward_views(const float* means3D, const float* shs, const float* shs_dc, const float* shs_rest,
+                                     int64_t P, int M, int sh_degree, const float* campos_views, const float* color_grads,
+                                     int n_views, float* grad_shs, float* grad_dc, float* grad_rest, float* grad_means3D,
+                                     int accumulate, cudaStream_t s);
 cudaError_t launch_image_loss(const float* color, const float* target, const float* invdepth, const float* prior,
                               const float* mask, int W, int H, float w_color, float w_depth, float* dL_dcolor,
                               float* dL_dinvdepth, float* loss, cudaStream_t s);

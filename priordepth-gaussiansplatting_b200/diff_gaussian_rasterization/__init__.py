@@ -98,6 +98,57 @@ class _RasterizeGaussians(torch.autograd.Function):
                 used(cov3Ds_precomp, grad_cov3Ds_precomp), None)
 
 
+class _RasterizeGaussiansFused(torch.autograd.Function):
+    """Extension: split SH (`dc` + `sh` = features_dc / features_rest, the pair render() passes
+    when separate_sh is set, /root/reference/gaussian_renderer/__init__.py:82-101) and/or raw parameters
+    (`raw_params=True`: opacities / scales / rotations are _opacity / _scaling / _rotation of
+    /root/reference/scene/gaussian_model.py:40-48 and the activations and their backward run inside the kernels)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, dc, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings, raw_params):
+        rs = raster_settings
+        num_rendered, color, radii, geom, binning, img, invdepths = _C.rasterize_gaussians(
+            rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh, rs.sh_degree,
+            rs.campos, rs.prefiltered, rs.antialiasing, rs.debug, dc=dc, raw_params=raw_params)
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.raw_params = bool(raw_params)
+        ctx.has_dc = dc is not None and dc.numel() != 0
+        ctx.binning_capacity = getattr(binning, "_pdgs_capacity", 0)
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities, geom,
+                              binning, img, dc if ctx.has_dc else torch.empty(0, device=means3D.device))
+        ctx.mark_non_differentiable(radii)
+        ctx.set_materialize_grads(False)
+        return color, radii, invdepths
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii, grad_out_invdepth):
+        rs = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities, geom, binning, img,
+         dc) = ctx.saved_tensors
+        binning._pdgs_capacity = ctx.binning_capacity
+        if grad_out_color is None:
+            grad_out_color = torch.zeros(3, rs.image_height, rs.image_width, dtype=torch.float32,
+                                         device=means3D.device)
+        res = _C.rasterize_gaussians_backward(
+            rs.bg, means3D, radii, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, grad_out_invdepth, sh, rs.sh_degree,
+            rs.campos, geom, ctx.num_rendered, binning, img, rs.antialiasing, rs.debug,
+            dc=dc if ctx.has_dc else None, raw_params=ctx.raw_params)
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+         grad_rotations) = res[:8]
+        grad_dc = res[8] if ctx.has_dc else None
+
+        def used(t, g):
+            return g if (t is not None and t.numel() != 0) else None
+
+        return (grad_means3D, grad_means2D, grad_dc, used(sh, grad_sh), used(colors_precomp, grad_colors_precomp),
+                grad_opacities.view_as(opacities), used(scales, grad_scales), used(rotations, grad_rotations),
+                used(cov3Ds_precomp, grad_cov3Ds_precomp), None, None)
+
+
 class GaussianRasterizer(nn.Module):
     def __init__(self, raster_settings):
         super().__init__()
@@ -109,8 +160,12 @@ class GaussianRasterizer(nn.Module):
             return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
-                cov3D_precomp=None):
+                cov3D_precomp=None, dc=None, raw_params=False):
+        """`dc` (features_dc, with `shs` = features_rest) and `raw_params` are extensions, see
+        _RasterizeGaussiansFused; without them this is the pinned reference module's signature."""
         rs = self.raster_settings
+        if dc is not None and colors_precomp is None and shs is None and dc.shape[0] == means3D.shape[0]:
+            shs = torch.empty(means3D.shape[0], 0, 3, dtype=torch.float32, device=means3D.device)  # degree-0 model
         if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
         if ((scales is None or rotations is None) and cov3D_precomp is None) or (
@@ -122,5 +177,8 @@ class GaussianRasterizer(nn.Module):
         scales = empty if scales is None else scales
         rotations = empty if rotations is None else rotations
         cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
+        if dc is not None or raw_params:
+            return _RasterizeGaussiansFused.apply(means3D, means2D, dc, shs, colors_precomp, opacities, scales, rotations,
+                                                  cov3D_precomp, rs, bool(raw_params))
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
                                    rs)

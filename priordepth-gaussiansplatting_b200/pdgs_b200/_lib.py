@@ -32,7 +32,8 @@ class PdgsCamera(C.Structure):
 
 class PdgsScene(C.Structure):
     _fields_ = [("P", C.c_int64), ("M", C.c_int32), ("means3D", vp), ("shs", vp), ("colors_precomp", vp),
-                ("opacities", vp), ("scales", vp), ("rotations", vp), ("cov3D_precomp", vp)]
+                ("opacities", vp), ("scales", vp), ("rotations", vp), ("cov3D_precomp", vp), ("shs_dc", vp),
+                ("shs_rest", vp), ("raw_params", C.c_int32)]
 
 
 class PdgsState(C.Structure):
@@ -47,7 +48,8 @@ class PdgsForwardOut(C.Structure):
 class PdgsGrads(C.Structure):
     _fields_ = [("means3D", vp), ("means2D", vp), ("shs", vp), ("colors_precomp", vp), ("opacities", vp),
                 ("scales", vp), ("rotations", vp), ("cov3D_precomp", vp), ("accumulate", C.c_int32),
-                ("densify_grad_accum", vp), ("densify_denom", vp), ("max_radii2D", vp), ("color_grad_view", vp)]
+                ("densify_grad_accum", vp), ("densify_denom", vp), ("max_radii2D", vp), ("color_grad_view", vp),
+                ("shs_dc", vp), ("shs_rest", vp)]
 
 
 class PdgsStateView(C.Structure):
@@ -78,6 +80,8 @@ SYMBOLS = {
     "pdgs_backward": (C.c_int, [vp, C.POINTER(PdgsScene), C.POINTER(PdgsCamera), C.POINTER(PdgsState), vp,
                                 C.c_int64, vp, vp, vp, C.c_size_t, C.POINTER(PdgsGrads), vp]),
     "pdgs_sh_backward_views": (C.c_int, [vp, C.POINTER(PdgsScene), C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int32, vp]),
+    "pdgs_sh_backward_views_split": (C.c_int, [vp, C.POINTER(PdgsScene), C.c_int32, vp, vp, C.c_int32, vp, vp, vp, C.c_int32,
+                                               vp]),
     "pdgs_mark_visible": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp]),
     "pdgs_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "pdgs_sort_pairs": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int32, vp, C.c_size_t, vp]),

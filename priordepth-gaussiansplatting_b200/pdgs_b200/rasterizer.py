@@ -64,11 +64,19 @@ def _camera(bg, scale_modifier, viewmatrix, projmatrix, tanfovx, tanfovy, H, W, 
     return cam
 
 
-def _scene(P, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp) -> L.PdgsScene:
+def _scene(P, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp, dc=None,
+           raw_params=False) -> L.PdgsScene:
+    """dc given: split SH -- `dc` is features_dc [P,1,3] and `sh` features_rest [P,M-1,3] (may be None/empty)."""
     sc = L.PdgsScene()
     sc.P = int(P)
-    sc.M = int(sh.shape[1]) if sh is not None else 0
-    sc.means3D, sc.shs, sc.colors_precomp = _ptr(means3D), _ptr(sh), _ptr(colors_precomp)
+    if dc is not None:
+        sc.M = 1 + (int(sh.shape[1]) if sh is not None else 0)
+        sc.shs_dc, sc.shs_rest, sc.shs = _ptr(dc), _ptr(sh), None
+    else:
+        sc.M = int(sh.shape[1]) if sh is not None else 0
+        sc.shs = _ptr(sh)
+    sc.raw_params = int(bool(raw_params))
+    sc.means3D, sc.colors_precomp = _ptr(means3D), _ptr(colors_precomp)
     sc.opacities, sc.scales, sc.rotations = _ptr(opacities), _ptr(scales), _ptr(rotations)
     sc.cov3D_precomp = _ptr(cov3D_precomp)
     return sc
@@ -91,8 +99,13 @@ def _binning_capacity(binning: Optional[torch.Tensor]) -> int:
 
 def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, sh, sh_degree, campos,
-                        prefiltered, antialiasing, debug):
-    """-> (num_rendered, color[3,H,W], radii[P] int32, geomBuffer, binningBuffer, imgBuffer, invdepths[1,H,W])."""
+                        prefiltered, antialiasing, debug, dc=None, raw_params=False):
+    """-> (num_rendered, color[3,H,W], radii[P] int32, geomBuffer, binningBuffer, imgBuffer, invdepths[1,H,W]).
+
+    Extensions beyond the reference's 20 arguments: `dc` = features_dc [P,1,3], in which case
+    `sh` is features_rest [P,M-1,3] (the pair render() passes when separate_sh is set,
+    /root/reference/gaussian_renderer/__init__.py:82-101); `raw_params` = opacities / scales / rotations are the
+    pre-activation parameters and sigmoid / exp / normalize run inside the preprocess kernel."""
     global LAUNCHES_FORWARD
     if means3D.dim() != 2 or means3D.shape[1] != 3:
         raise L.PdgsError("means3D must have dimensions (num_points, 3)")
@@ -103,6 +116,7 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
     P, H, W = means3D.shape[0], int(image_height), int(image_width)
     means3D = _f32c(means3D, "means3D", dev)
     sh = _f32c(sh, "sh", dev)
+    dc = _f32c(dc, "dc", dev)
     colors_precomp = _f32c(colors_precomp, "colors_precomp", dev)
     opacities = _f32c(opacities, "opacities", dev)
     scales = _f32c(scales, "scales", dev)
@@ -114,6 +128,8 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
     campos = _f32c(campos, "campos", dev)
     if sh is not None and sh.dim() != 3:
         raise L.PdgsError("sh must have dimensions (num_points, num_coeffs, 3)")
+    if dc is not None and (dc.dim() != 3 or dc.shape[1] != 1 or dc.shape[0] != P):
+        raise L.PdgsError("dc must have dimensions (num_points, 1, 3)")
     with torch.cuda.device(dev):
         h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
         stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
@@ -129,7 +145,7 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
             binning = torch.empty(lib.pdgs_binning_bytes(cap, P), **u8)
         cam = _camera(bg, scale_modifier, viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh_degree, campos,
                       prefiltered, antialiasing, debug)
-        sc = _scene(P, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp)
+        sc = _scene(P, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp, dc, raw_params)
         st = _state(geom, image, binning, cap)
         out = L.PdgsForwardOut(_ptr(color), _ptr(invdepth), _ptr(radii))
         R = C.c_int64(0)
@@ -159,12 +175,15 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
 def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tanfovx, tanfovy, grad_out_color,
                                  grad_out_invdepth, sh, sh_degree, campos, geomBuffer, num_rendered, binningBuffer,
-                                 imgBuffer, antialiasing, debug, accumulate_into: Optional[dict] = None):
+                                 imgBuffer, antialiasing, debug, accumulate_into: Optional[dict] = None, dc=None,
+                                 raw_params=False):
     """-> (grad_means2D[P,3], grad_colors_precomp[P,3], grad_opacities[P,1], grad_means3D[P,3],
            grad_cov3Ds_precomp[P,6], grad_sh[P,M,3], grad_scales[P,3], grad_rotations[P,4]).
 
     accumulate_into (extension used by the view-parallel path): a dict of preallocated gradient
-    tensors keyed like PdgsGrads; the kernel adds into them instead of writing fresh tensors."""
+    tensors keyed like PdgsGrads; the kernel adds into them instead of writing fresh tensors.
+    dc / raw_params: as in rasterize_gaussians; with `dc` the tuple gains a ninth element grad_dc[P,1,3] and grad_sh is
+    the gradient of features_rest; with raw_params the opacity / scale / rotation gradients are w.r.t. the raw tensors."""
     global LAUNCHES_BACKWARD
     lib = L.lib()
     dev = means3D.device
@@ -172,6 +191,7 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
     H, W = int(grad_out_color.shape[-2]), int(grad_out_color.shape[-1])
     means3D = _f32c(means3D, "means3D", dev)
     sh = _f32c(sh, "sh", dev)
+    dc = _f32c(dc, "dc", dev)
     colors_precomp = _f32c(colors_precomp, "colors_precomp", dev)
     opacities = _f32c(opacities, "opacities", dev)
     scales = _f32c(scales, "scales", dev)
@@ -196,6 +216,7 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
             dopac = torch.empty(P, 1, **f32)
             dcolors = torch.empty(P, 3, **f32) if colors_precomp is not None else torch.zeros(P, 3, **f32)
             dsh = torch.empty(P, M, 3, **f32) if sh is not None else torch.zeros(P, 0, 3, **f32)
+            ddc = torch.empty(P, 1, 3, **f32) if dc is not None else None
             dcov = torch.empty(P, 6, **f32) if cov3D_precomp is not None else torch.zeros(P, 6, **f32)
             dscales = torch.empty(P, 3, **f32) if scales is not None else torch.zeros(P, 3, **f32)
             drots = torch.empty(P, 4, **f32) if rotations is not None else torch.zeros(P, 4, **f32)
@@ -205,8 +226,15 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
             dmeans2D, dmeans3D, dopac = a.get("means2D"), a.get("means3D"), a.get("opacities")
             dcolors, dsh, dcov = a.get("colors_precomp"), a.get("shs"), a.get("cov3D_precomp")
             dscales, drots = a.get("scales"), a.get("rotations")
+            ddc = a.get("shs_dc")
+            if dc is not None:
+                dsh = a.get("shs_rest")
             g.accumulate = 1
-        g.means3D, g.means2D, g.shs = _ptr(dmeans3D), _ptr(dmeans2D), _ptr(dsh) if sh is not None else None
+        g.means3D, g.means2D = _ptr(dmeans3D), _ptr(dmeans2D)
+        if dc is not None:
+            g.shs_dc, g.shs_rest = _ptr(ddc), _ptr(dsh)
+        else:
+            g.shs = _ptr(dsh) if sh is not None else None
         g.colors_precomp = _ptr(dcolors) if colors_precomp is not None else None
         g.opacities = _ptr(dopac)
         g.scales = _ptr(dscales) if scales is not None else None
@@ -217,18 +245,46 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
             g.densify_denom = _ptr(accumulate_into.get("densify_denom"))
             g.max_radii2D = _ptr(accumulate_into.get("max_radii2D"))
             # deferred SH backward (sh_backward_views): this view only leaves its masked dL/drgb [P,3]
-            g.color_grad_view = _ptr(accumulate_into.get("color_grad_view")) if sh is not None else None
+            g.color_grad_view = (_ptr(accumulate_into.get("color_grad_view"))
+                                 if (sh is not None or dc is not None) else None)
         if P > 0:
             scratch = torch.empty(lib.pdgs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
             cam = _camera(bg, scale_modifier, viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh_degree, campos,
                           False, antialiasing, debug)
-            sc = _scene(P, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp)
+            sc = _scene(P, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp, dc, raw_params)
             st = _state(geomBuffer, imgBuffer, binningBuffer, _binning_capacity(binningBuffer))
             L.check(lib.pdgs_backward(h, C.byref(sc), C.byref(cam), C.byref(st), _ptr(radii), int(num_rendered),
                                       _ptr(grad_out_color), _ptr(grad_out_invdepth), _ptr(scratch), scratch.numel(),
                                       C.byref(g), stream), "pdgs_backward")
             LAUNCHES_BACKWARD = 2 if num_rendered > 0 else 1
+    if dc is not None:
+        return dmeans2D, dcolors, dopac, dmeans3D, dcov, dsh, dscales, drots, ddc
     return dmeans2D, dcolors, dopac, dmeans3D, dcov, dsh, dscales, drots
+
+
+def sh_backward_views_split(means3D, dc, rest, sh_degree, campos_views, color_grads, grad_dc, grad_rest, grad_means3D,
+                            accumulate=True):
+    """sh_backward_views for a scene given as features_dc [P,1,3] / features_rest [P,M-1,3]
+    (C ABI pdgs_sh_backward_views_split)."""
+    global LAUNCHES_SH_BWD
+    lib = L.lib()
+    dev = means3D.device
+    if not means3D.is_cuda:
+        raise L.PdgsError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
+    means3D, dc, rest = _f32c(means3D, "means3D", dev), _f32c(dc, "dc", dev), _f32c(rest, "rest", dev)
+    campos_views, color_grads = _f32c(campos_views, "campos_views", dev), _f32c(color_grads, "color_grads", dev)
+    P, V = means3D.shape[0], int(campos_views.shape[0])
+    if color_grads.numel() != V * P * 3:
+        raise L.PdgsError("color_grads must be [V,P,3]")
+    with torch.cuda.device(dev):
+        h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        sc = _scene(P, means3D, rest, None, None, None, None, None, dc)
+        L.check(lib.pdgs_sh_backward_views_split(h, C.byref(sc), int(sh_degree), _ptr(campos_views), _ptr(color_grads), V,
+                                                 _ptr(grad_dc), _ptr(grad_rest), _ptr(grad_means3D), int(bool(accumulate)),
+                                                 stream), "pdgs_sh_backward_views_split")
+        LAUNCHES_SH_BWD = (V + 255) // 256
+    return grad_dc, grad_rest, grad_means3D
 
 
 def sh_backward_views(means3D, sh, sh_degree, campos_views, color_grads, grad_shs, grad_means3D, accumulate=True):
