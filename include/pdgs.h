@@ -140,7 +140,7 @@ enum {
   PDGS_STAGE_PREPROCESS = 0, PDGS_STAGE_SCAN = 1, PDGS_STAGE_DUPLICATE = 2, PDGS_STAGE_SORT = 3,
   PDGS_STAGE_RANGES = 4, PDGS_STAGE_BLEND_FWD = 5, PDGS_STAGE_BWD_ZERO = 6, PDGS_STAGE_BLEND_BWD = 7,
   PDGS_STAGE_PREPROCESS_BWD = 8, PDGS_STAGE_LOSS = 9, PDGS_STAGE_DEPTH_SORT = 10, PDGS_STAGE_SH_BWD = 11,
-  PDGS_STAGE_COUNT = 12
+  PDGS_STAGE_ADAM = 12, PDGS_STAGE_COUNT = 13
 };
 int pdgs_set_stage_timing(PdgsHandle* h, int32_t enable);
 int pdgs_stage_times(PdgsHandle* h, float* ms_sum, int32_t* counts, int32_t n);
@@ -213,6 +213,27 @@ int pdgs_image_loss_ssim(PdgsHandle* h, const float* color, const float* target,
                          const float* prior, const float* mask, int32_t width, int32_t height, float lambda_dssim,
                          float w_depth, void* scratch, size_t scratch_bytes, float* dL_dcolor, float* dL_dinvdepth,
                          float* loss, void* stream);
+
+/* Visibility-sparse Adam: the kernel under `SparseGaussianAdam.step(visibility, N)`, which the reference uses when the
+ * rasterizer package exports that class (/root/reference/train.py:47-52, 332-334; scene/gaussian_model.py:25-28,
+ * 196-198; the class itself lives in the accelerated rasterizer branch, absent from /root/reference).  For every
+ * parameter group (tensor [N, M], row i = Gaussian i) and every row with visible[i] != 0 (or radii[i] > 0 when
+ * `visible` is NULL):
+ *   m = b1*m + (1-b1)*g;  v = b2*v + (1-b2)*g*g;  p -= lr * m / (sqrt(v) + eps)                      (step == 0)
+ *   p -= (lr / (1 - b1^step)) * m / (sqrt(v) / sqrt(1 - b2^step) + eps)   (step > 0: torch.optim.Adam's correction)
+ * Rows of invisible Gaussians are neither read nor written.  All groups (<= 8) are updated by one launch.  Arithmetic
+ * is fp32; the scalars arrive as doubles so that step > 0 can round (1 - beta), lr / (1 - b1^step) and
+ * sqrt(1 - b2^step) to fp32 once, as torch does, while step == 0 forms (1.0f - beta) in fp32 like the upstream kernel. */
+typedef struct PdgsAdamGroup {
+  float* param;        /* [N,M] updated in place */
+  const float* grad;   /* [N,M] */
+  float* exp_avg;      /* [N,M] */
+  float* exp_avg_sq;   /* [N,M] */
+  double lr;
+  int32_t M;           /* floats per Gaussian in this tensor */
+} PdgsAdamGroup;
+int pdgs_sparse_adam(PdgsHandle* h, const PdgsAdamGroup* groups, int32_t n_groups, const uint8_t* visible,
+                     const int32_t* radii, int64_t N, double beta1, double beta2, double eps, int32_t step, void* stream);
 
 int pdgs_mark_visible(const float* means3D, const float* viewmatrix, const float* projmatrix, int64_t P,
                       uint8_t* present, void* stream);

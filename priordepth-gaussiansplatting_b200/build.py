@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(OUT_DIR, "libpdgs.so")
-SOURCES = ["pdgs_preprocess.cu", "pdgs_binning.cu", "pdgs_render.cu", "pdgs_loss.cu", "pdgs_ssim.cu", "pdgs_capi.cu"]
+SOURCES = ["pdgs_preprocess.cu", "pdgs_binning.cu", "pdgs_render.cu", "pdgs_loss.cu", "pdgs_ssim.cu", "pdgs_optim.cu", "pdgs_capi.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
          "-Xcompiler", "-ffp-contract=off", "--expt-relaxed-constexpr"] + os.environ.get("PDGS_NVCC_FLAGS", "").split()

@@ -435,6 +435,25 @@ int pdgs_sh_backward_views_split(PdgsHandle* h, const PdgsScene* scene, int32_t 
   return PDGS_OK;
 }
 
+int pdgs_sparse_adam(PdgsHandle* h, const PdgsAdamGroup* groups, int32_t n_groups, const uint8_t* visible,
+                     const int32_t* radii, int64_t N, double beta1, double beta2, double eps, int32_t step, void* stream) {
+  if (!h || n_groups < 0 || N < 0 || step < 0) return fail(PDGS_E_INVALID, "pdgs_sparse_adam: bad argument");
+  if (n_groups == 0 || N == 0) return PDGS_OK;
+  if (!groups || n_groups > ADAM_MAX_GROUPS) return fail(PDGS_E_INVALID, "pdgs_sparse_adam: 1..8 groups");
+  if (!visible && !radii) return fail(PDGS_E_INVALID, "pdgs_sparse_adam: visible or radii must be given");
+  AdamGroup g[ADAM_MAX_GROUPS];
+  for (int i = 0; i < n_groups; ++i) {
+    if (!groups[i].param || !groups[i].grad || !groups[i].exp_avg || !groups[i].exp_avg_sq || groups[i].M < 1)
+      return fail(PDGS_E_INVALID, "pdgs_sparse_adam: NULL tensor or M < 1 in a group");
+    g[i].param = groups[i].param; g[i].grad = groups[i].grad; g[i].exp_avg = groups[i].exp_avg;
+    g[i].exp_avg_sq = groups[i].exp_avg_sq; g[i].lr_host = groups[i].lr; g[i].lr = 0.f; g[i].M = groups[i].M; g[i].vec4 = 0;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  StageTimer t(h, PDGS_STAGE_ADAM, s);
+  PD_CUDA(launch_sparse_adam(g, n_groups, visible, radii, N, beta1, beta2, eps, step, s));
+  return PDGS_OK;
+}
+
 int pdgs_mark_visible(const float* means3D, const float* viewmatrix, const float* projmatrix, int64_t P,
                       uint8_t* present, void* stream) {
   (void)projmatrix;

@@ -224,6 +224,17 @@ cudaError_t launch_ssim_backward(const float* img1, const float* img2, const flo
                                  const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, int planes, int W,
                                  int H, float l1_weight, float* dL_dimg1, const double* fin_sums, double fin_scale,
                                  float* fin_ssim, float* fin_l1, cudaStream_t s);
+// Visibility-sparse Adam (pdgs_optim.cu).  One group = one parameter tensor [N, M] with its gradient and moments.
+constexpr int ADAM_MAX_GROUPS = 8;
+struct AdamGroup {
+  float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+  double lr_host;  // caller's learning rate; launch_sparse_adam derives the fp32 step size `lr`
+  float lr; int M; int vec4;
+};
+// visible [N] bytes, or (visible == NULL) radii [N] with visible = radii > 0.  step > 0: torch.optim.Adam bias
+// correction for that step count; step == 0: none (the upstream sparse kernel's rule).
+cudaError_t launch_sparse_adam(const AdamGroup* groups, int n_groups, const uint8_t* visible, const int32_t* radii,
+                               int64_t N, double b1, double b2, double eps, int step, cudaStream_t s);
 cudaError_t launch_mark_visible(const float* means3D, const float* viewmatrix, int64_t P, uint8_t* present,
                                 cudaStream_t s);
 

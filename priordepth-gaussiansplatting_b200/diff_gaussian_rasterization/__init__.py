@@ -8,9 +8,12 @@ Mirrors the Python surface the reference imports at
 `rasterize_gaussians_backward`, `mark_visible` (the reference
 module's own source is absent from /root/reference).
 
-Deliberately NOT exported: `SparseGaussianAdam`, `_C.fusedssim` -- the reference probes for
-them with try/except (/root/reference/train.py:47-52, utils/loss_utils.py:16-19) and must keep
-taking the dense-Adam / `separate_sh=False` path of the pinned rasterizer commit.
+`SparseGaussianAdam` IS exported (pdgs_b200/optim.py over pdgs_sparse_adam): the reference probes for it with
+try/except (/root/reference/train.py:47-52, scene/gaussian_model.py:25-28, render.py:23-27) and, finding it, calls
+render(..., separate_sh=True), i.e. `GaussianRasterizer.forward(dc=..., shs=features_rest)` -- which this package
+implements -- and uses the sparse optimiser when `--optimizer_type sparse_adam` is given.  Set PDGS_NO_SPARSE_ADAM=1 to
+hide the class and reproduce the pinned commit's import behaviour (separate_sh=False, dense Adam).  `_C.fusedssim` lives in the
+separate `fused_ssim` package, as in the reference.
 """
 from __future__ import annotations
 
@@ -27,6 +30,8 @@ if _PKG_ROOT not in sys.path:
     sys.path.insert(0, _PKG_ROOT)
 
 from pdgs_b200 import rasterizer as _impl  # noqa: E402
+if os.environ.get("PDGS_NO_SPARSE_ADAM", "0") != "1":  # "1": look exactly like the pinned commit (separate_sh stays False)
+    from pdgs_b200.optim import SparseGaussianAdam  # noqa: E402,F401
 
 _C = types.ModuleType(__name__ + "._C")
 _C.rasterize_gaussians = _impl.rasterize_gaussians

@@ -52,6 +52,10 @@ class PdgsGrads(C.Structure):
                 ("shs_dc", vp), ("shs_rest", vp)]
 
 
+class PdgsAdamGroup(C.Structure):
+    _fields_ = [("param", vp), ("grad", vp), ("exp_avg", vp), ("exp_avg_sq", vp), ("lr", C.c_double), ("M", C.c_int32)]
+
+
 class PdgsStateView(C.Structure):
     _fields_ = [("point_list", vp), ("sorted_tiles", vp), ("ranges", vp), ("final_T", vp), ("n_contrib", vp), ("n_tested", vp), ("n_accepted", vp),
                 ("tiles_touched", vp), ("point_offsets", vp), ("depth_order", vp), ("xy", vp), ("conic_opacity", vp), ("rgb", vp)]
@@ -82,6 +86,8 @@ SYMBOLS = {
     "pdgs_sh_backward_views": (C.c_int, [vp, C.POINTER(PdgsScene), C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int32, vp]),
     "pdgs_sh_backward_views_split": (C.c_int, [vp, C.POINTER(PdgsScene), C.c_int32, vp, vp, C.c_int32, vp, vp, vp, C.c_int32,
                                                vp]),
+    "pdgs_sparse_adam": (C.c_int, [vp, C.POINTER(PdgsAdamGroup), C.c_int32, vp, vp, C.c_int64, C.c_double, C.c_double, C.c_double,
+                                   C.c_int32, vp]),
     "pdgs_mark_visible": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp]),
     "pdgs_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "pdgs_sort_pairs": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int32, vp, C.c_size_t, vp]),
@@ -89,7 +95,7 @@ SYMBOLS = {
 }
 
 STAGES = ("preprocess", "scan", "duplicate", "sort", "ranges", "blend_fwd", "bwd_zero", "blend_bwd", "preprocess_bwd", "loss",
-          "depth_sort", "sh_bwd")
+          "depth_sort", "sh_bwd", "adam")
 
 _lib = None
 _lock = threading.Lock()

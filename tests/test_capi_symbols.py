@@ -78,7 +78,10 @@ def test_python_api_surface_and_argument_validation(lib):
         "sh_degree", "campos", "prefiltered", "debug", "antialiasing")
     for name in ("rasterize_gaussians", "rasterize_gaussians_backward", "mark_visible"):
         assert callable(getattr(dgr._C, name))
-    assert not hasattr(dgr, "SparseGaussianAdam") and not hasattr(dgr._C, "fusedssim")
+    # the accelerated-rasterizer surface the reference probes for (train.py:47-52); fusedssim lives in fused_ssim
+    assert issubclass(dgr.SparseGaussianAdam, torch.optim.Adam) and not hasattr(dgr._C, "fusedssim")
+    import inspect
+    assert {"dc", "raw_params"} <= set(inspect.signature(dgr.GaussianRasterizer.forward).parameters)
     rs = dgr.GaussianRasterizationSettings(16, 16, 0.5, 0.5, torch.zeros(3), 1.0, torch.eye(4), torch.eye(4), 3,
                                            torch.zeros(3), False, False, False)
     r = dgr.GaussianRasterizer(raster_settings=rs)
