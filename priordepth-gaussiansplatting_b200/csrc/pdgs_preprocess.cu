@@ -99,8 +99,11 @@ __device__ __forceinline__ void warp_stage_rest(const float* __restrict__ rest, 
   __syncwarp();
 }
 
+#ifndef PDGS_PRE_CTAS
+#define PDGS_PRE_CTAS 3
+#endif
 template <bool SPLIT>
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(DeviceArgs a, GeomView g, int32_t* __restrict__ radii) {
+__global__ void __launch_bounds__(PRE_THREADS, PDGS_PRE_CTAS) preprocess_kernel(DeviceArgs a, GeomView g, int32_t* __restrict__ radii) {
   __shared__ Camera cam;
   extern __shared__ __align__(16) float pre_stage[];  // SPLIT && M == 16: [warps][32 * 45]
   load_camera(a, &cam);

@@ -9,9 +9,9 @@ python $PKG/build.py > /dev/null
 base=${src%.cu}
 mkdir -p $PKG/lib/var
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -ffp-contract=off \
-  --expt-relaxed-constexpr "$@" -Xptxas -v -c $PKG/csrc/$src -o $PKG/lib/var/${base}_$name.o 2>&1 | grep -A2 "render_\|Compiling.*$KERNEL" | grep -i "registers\|spill" || true
+  --expt-relaxed-constexpr "$@" -Xptxas -v -c $PKG/csrc/$src -o $PKG/lib/var/${base}_$name.o 2>&1 | grep -A2 "Compiling.*${KERNEL:-render_}" | grep -i "registers\|spill" || true
 objs=""
-for o in pdgs_preprocess pdgs_binning pdgs_render pdgs_loss pdgs_capi; do
+for o in pdgs_preprocess pdgs_binning pdgs_render pdgs_loss pdgs_ssim pdgs_optim pdgs_capi; do
   if [ "$o" == "$base" ]; then objs="$objs $PKG/lib/var/${base}_$name.o"; else objs="$objs $PKG/lib/$o.o"; fi
 done
 /usr/local/cuda/bin/nvcc -shared -o $PKG/lib/libpdgs_$name.so $objs -gencode arch=compute_100a,code=sm_100a -lcudart
