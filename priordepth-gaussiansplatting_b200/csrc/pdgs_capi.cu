@@ -213,7 +213,7 @@ static int run_binning_and_blend(PdgsHandle* h, const DeviceArgs& a, GeomView g,
   }
   {
     StageTimer t(h, PDGS_STAGE_BLEND_FWD, s);
-    PD_STEP(debug, s, launch_render_forward(a, g, im, b.point_list, st->capacity_pairs, out->color, out->invdepth, s));
+    PD_STEP(debug, s, launch_render_forward(a, g, im, b.point_list, b.pair_mask, st->capacity_pairs, out->color, out->invdepth, s));
   }
   return PDGS_OK;
 }
@@ -295,7 +295,7 @@ int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, 
     if (!state->binning) return fail(PDGS_E_INVALID, "binning buffer is NULL");
     BinningView b = carve_binning(state->binning, state->capacity_pairs);
     StageTimer t(h, PDGS_STAGE_BLEND_BWD, s);
-    PD_STEP(debug, s, launch_render_backward(a, g, im, b.point_list, dL_dcolor, dL_dinvdepth, acc, s));
+    PD_STEP(debug, s, launch_render_backward(a, g, im, b.point_list, b.pair_mask, dL_dcolor, dL_dinvdepth, acc, s));
   }
   GradPtrs gp;
   gp.means3D = grads->means3D; gp.means2D = grads->means2D; gp.shs = grads->shs;

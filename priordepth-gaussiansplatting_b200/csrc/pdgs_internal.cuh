@@ -131,6 +131,7 @@ struct BinningView {
   uint32_t* tkeys_a;     // [cap] sorted tile ids (buffer A keys)
   uint32_t* tkeys_b;     // [cap]
   uint32_t* vals_b;      // [cap]
+  uint8_t* pair_mask;    // [cap] per sorted pair: 8x4-pixel patches of its tile the Gaussian reaches (forward -> backward)
   void* sort_scratch;
   size_t sort_scratch_bytes;
   size_t bytes;
@@ -152,6 +153,7 @@ inline __host__ BinningView carve_binning(void* base, int64_t capacity) {
   v.tkeys_a = (uint32_t*)(p + off); off += align_up(cap * sizeof(uint32_t));
   v.tkeys_b = (uint32_t*)(p + off); off += align_up(cap * sizeof(uint32_t));
   v.vals_b = (uint32_t*)(p + off); off += align_up(cap * sizeof(uint32_t));
+  v.pair_mask = (uint8_t*)(p + off); off += align_up(cap);
   SortScratch s = carve_sort_scratch(nullptr, capacity, SORT_THREADS * SORT_ITEMS_U32, 4);
   v.sort_scratch = (void*)(p + off);
   v.sort_scratch_bytes = s.bytes;
@@ -194,9 +196,9 @@ cudaError_t launch_sort_u64(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b
 cudaError_t launch_ranges(const uint32_t* tkeys, const uint32_t* n_dev, int64_t capacity, uint2* ranges, int tiles,
                           cudaStream_t s);
 cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
-                                  int64_t capacity, float* out_color, float* out_invdepth, cudaStream_t s);
+                                  uint8_t* pair_mask, int64_t capacity, float* out_color, float* out_invdepth, cudaStream_t s);
 cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
-                                   const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s);
+                                   uint8_t* pair_mask, const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s);
 struct GradPtrs {
   float* means3D; float* means2D; float* shs; float* colors_precomp; float* opacities; float* scales;
   float* rotations; float* cov3D_precomp; int accumulate;

@@ -112,19 +112,29 @@ struct Stage {          // 49 bytes per staged list entry
   uint8_t mask[RT];     // warp patches the Gaussian can reach
 };
 
-// Stage list entry `src` (or nothing when !valid) into slot threadIdx.x.
+// Stage list entry `src` (or nothing when !valid) into slot threadIdx.x.  The forward (REUSE = false) computes the
+// patch mask and leaves it in pair_mask[src]; the backward (REUSE = true) reads it back instead of recomputing it and
+// does not gather the records of an entry that reaches no patch (35 % of the pairs on C4).
+template <bool REUSE>
 __device__ __forceinline__ void stage_entry(Stage& st, bool valid, uint32_t src, const float4* __restrict__ gA,
                                             const float4* __restrict__ gB, const float4* __restrict__ gC,
-                                            const uint32_t* __restrict__ point_list, float tx0, float ty0) {
+                                            const uint32_t* __restrict__ point_list, uint8_t* __restrict__ pair_mask,
+                                            float tx0, float ty0) {
   uint32_t m = 0;
   if (valid) {
-    const uint32_t id = __ldg(point_list + src);
-    const float4 a = __ldg(gA + id), b = __ldg(gB + id), c = __ldg(gC + id);
-    const float L = __log2f(b.y);
-    st.a[threadIdx.x] = make_float4(a.x, a.y, (-0.5f * LOG2E) * a.z, -LOG2E * a.w);
-    st.b[threadIdx.x] = make_float4((-0.5f * LOG2E) * b.x, L, b.z, c.x);
-    st.c[threadIdx.x] = make_float4(c.y, c.z, __uint_as_float(id), 0.f);
-    m = patch_mask(a.x, a.y, a.z, a.w, b.x, b.y, L, tx0, ty0);
+    if (REUSE) m = pair_mask[src];
+    if (!REUSE || m != 0) {
+      const uint32_t id = __ldg(point_list + src);
+      const float4 a = __ldg(gA + id), b = __ldg(gB + id), c = __ldg(gC + id);
+      const float L = __log2f(b.y);
+      st.a[threadIdx.x] = make_float4(a.x, a.y, (-0.5f * LOG2E) * a.z, -LOG2E * a.w);
+      st.b[threadIdx.x] = make_float4((-0.5f * LOG2E) * b.x, L, b.z, c.x);
+      st.c[threadIdx.x] = make_float4(c.y, c.z, __uint_as_float(id), 0.f);
+      if (!REUSE) {
+        m = patch_mask(a.x, a.y, a.z, a.w, b.x, b.y, L, tx0, ty0);
+        pair_mask[src] = (uint8_t)m;
+      }
+    }
   }
   st.mask[threadIdx.x] = (uint8_t)m;
 }
@@ -135,7 +145,8 @@ __device__ __forceinline__ void stage_entry(Stage& st, bool valid, uint32_t src,
 __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
                                                             const float4* __restrict__ gC,
                                                             const uint2* __restrict__ ranges,
-                                                            const uint32_t* __restrict__ point_list, int W, int H,
+                                                            const uint32_t* __restrict__ point_list,
+                                                            uint8_t* __restrict__ pair_mask, int W, int H,
                                                             const float* __restrict__ bg, float* __restrict__ out_color,
                                                             float* __restrict__ out_invdepth, float* __restrict__ final_T,
                                                             uint32_t* __restrict__ n_contrib,
@@ -155,7 +166,7 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
   bool done = !inside;
   for (uint32_t base = range.x; base < range.y; base += RT) {
     if (__syncthreads_count(done) == RT) break;
-    stage_entry(st, base + threadIdx.x < range.y, base + threadIdx.x, gA, gB, gC, point_list, tx0, ty0);
+    stage_entry<false>(st, base + threadIdx.x < range.y, base + threadIdx.x, gA, gB, gC, point_list, pair_mask, tx0, ty0);
     __syncthreads();
     if (__all_sync(FULL, done)) continue;  // this warp's patch is finished; it only helps staging
     const int cnt = min((uint32_t)RT, range.y - base);
@@ -330,7 +341,8 @@ __device__ __forceinline__ void flush_panel(uint32_t wp, int count, int lane, fl
 __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
                                                                 const float4* __restrict__ gC,
                                                                 const uint2* __restrict__ ranges,
-                                                                const uint32_t* __restrict__ point_list, int W, int H,
+                                                                const uint32_t* __restrict__ point_list,
+                                                                uint8_t* __restrict__ pair_mask, int W, int H,
                                                                 const float* __restrict__ bg,
                                                                 const float* __restrict__ final_T,
                                                                 const uint32_t* __restrict__ n_contrib,
@@ -384,7 +396,7 @@ __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(cons
   for (uint32_t done = 0; done < todo; done += RT) {
     __syncthreads();
     const uint32_t progress = done + threadIdx.x;
-    stage_entry(st, progress < todo, range.x + (todo - 1 - progress), gA, gB, gC, point_list, tx0, ty0);
+    stage_entry<true>(st, progress < todo, range.x + (todo - 1 - progress), gA, gB, gC, point_list, pair_mask, tx0, ty0);
     __syncthreads();
     const int cnt = min((uint32_t)RT, todo - done);
     const uint32_t top = todo - 1 - done;  // list position of staged entry 0 (entries go back to front)
@@ -443,17 +455,17 @@ __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(cons
 }  // namespace
 
 cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
-                                  int64_t capacity, float* out_color, float* out_invdepth, cudaStream_t s) {
+                                  uint8_t* pair_mask, int64_t capacity, float* out_color, float* out_invdepth, cudaStream_t s) {
   (void)capacity;
   if (a.W <= 0 || a.H <= 0) return cudaSuccess;
   dim3 grid(a.grid_x, a.grid_y);
-  render_forward_kernel<<<grid, RT, 0, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, a.W, a.H, a.bg, out_color,
+  render_forward_kernel<<<grid, RT, 0, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, pair_mask, a.W, a.H, a.bg, out_color,
                                             out_invdepth, im.final_T, im.n_contrib, im.n_tested, im.n_accepted);
   return cudaGetLastError();
 }
 
 cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
-                                   const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
+                                   uint8_t* pair_mask, const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
   if (a.W <= 0 || a.H <= 0) return cudaSuccess;
   // 49.3 KB of dynamic shared memory per CTA (above the 48 KB static limit): opt in once per device
   static thread_local int configured_device = -1;
@@ -466,7 +478,7 @@ cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im
     configured_device = dev;
   }
   dim3 grid(a.grid_x, a.grid_y);
-  render_backward_kernel<<<grid, RT, BWD_SMEM, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, a.W, a.H, a.bg,
+  render_backward_kernel<<<grid, RT, BWD_SMEM, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, pair_mask, a.W, a.H, a.bg,
                                                     im.final_T, im.n_contrib, dL_dcolor, dL_dinvdepth, acc);
   return cudaGetLastError();
 }
