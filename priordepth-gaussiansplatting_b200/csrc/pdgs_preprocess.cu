@@ -365,6 +365,16 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
 // ------------------------------------------------------------------------------------------
 constexpr int PB_TILE = 256;
 
+// Accumulation into the per-Gaussian gradient rows (batch path) uses fire-and-forget reductions: the add happens in
+// L2 and the thread never waits for the old value (a load-add-store would put one more DRAM round trip at the end of
+// every thread of this latency-bound kernel).  Each row has one writer per launch, so the result is deterministic.
+__device__ __forceinline__ void red_add(float* p, float v) {
+  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_add4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 struct PbShared {  // the deferred-SH variant allocates only the part before sh_in
   float acc_in[PB_TILE * ACC_FLOATS];
   Camera cam;
@@ -388,8 +398,11 @@ struct ShRowSplit {  // split SH row in shared memory: 3 DC floats + 3(M-1) rest
 // SPLIT: the scene holds features_dc [P,3] and features_rest [P,3(M-1)] instead of one [P,3M] array.  The staging
 // regions sh_in / sh_out then hold the tile's rest block ([256][3(M-1)]) followed by its DC block ([256][3]) -- the
 // same 256*3M floats -- each moved by its own bulk copy.
+#ifndef PDGS_PB_DEFER_CTAS
+#define PDGS_PB_DEFER_CTAS 3
+#endif
 template <bool DEFER, bool SPLIT>
-__global__ void __launch_bounds__(PB_TILE, DEFER ? 3 : 2) preprocess_backward_sh_kernel(DeviceArgs a, GeomView g,
+__global__ void __launch_bounds__(PB_TILE, DEFER ? PDGS_PB_DEFER_CTAS : 2) preprocess_backward_sh_kernel(DeviceArgs a, GeomView g,
                                                                            const int32_t* __restrict__ radii,
                                                                            const float* __restrict__ acc, GradPtrs gp,
                                                                            int bulk_ok) {
@@ -566,7 +579,7 @@ __global__ void __launch_bounds__(PB_TILE, DEFER ? 3 : 2) preprocess_backward_sh
         if (gp.cov3D_precomp) {
 #pragma unroll
           for (int k = 0; k < 6; ++k) {
-            if (gp.accumulate) gp.cov3D_precomp[6 * idx + k] += g_cov[k]; else gp.cov3D_precomp[6 * idx + k] = g_cov[k];
+            if (gp.accumulate) red_add(gp.cov3D_precomp + 6 * idx + k, g_cov[k]); else gp.cov3D_precomp[6 * idx + k] = g_cov[k];
           }
         }
       } else {
@@ -576,34 +589,32 @@ __global__ void __launch_bounds__(PB_TILE, DEFER ? 3 : 2) preprocess_backward_sh
         if (gp.scales) {
 #pragma unroll
           for (int k = 0; k < 3; ++k) {
-            if (gp.accumulate) gp.scales[3 * idx + k] += g_scale[k]; else gp.scales[3 * idx + k] = g_scale[k];
+            if (gp.accumulate) red_add(gp.scales + 3 * idx + k, g_scale[k]); else gp.scales[3 * idx + k] = g_scale[k];
           }
         }
         if (gp.rotations) {
-          float4* dst = reinterpret_cast<float4*>(gp.rotations) + idx;
-          float4 v = make_float4(g_rot[0], g_rot[1], g_rot[2], g_rot[3]);
-          if (gp.accumulate) { const float4 o = *dst; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
-          *dst = v;
+          if (gp.accumulate) red_add4(gp.rotations + 4 * idx, g_rot[0], g_rot[1], g_rot[2], g_rot[3]);
+          else reinterpret_cast<float4*>(gp.rotations)[idx] = make_float4(g_rot[0], g_rot[1], g_rot[2], g_rot[3]);
         }
       }
       if (gp.means3D) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-          if (gp.accumulate) gp.means3D[3 * idx + k] += g_mean[k]; else gp.means3D[3 * idx + k] = g_mean[k];
+          if (gp.accumulate) red_add(gp.means3D + 3 * idx + k, g_mean[k]); else gp.means3D[3 * idx + k] = g_mean[k];
         }
       }
       if (gp.means2D) {
-        if (gp.accumulate) { gp.means2D[3 * idx] += in.g_mean2d_x; gp.means2D[3 * idx + 1] += in.g_mean2d_y; }
+        if (gp.accumulate) { red_add(gp.means2D + 3 * idx, in.g_mean2d_x); red_add(gp.means2D + 3 * idx + 1, in.g_mean2d_y); }
         else { gp.means2D[3 * idx] = in.g_mean2d_x; gp.means2D[3 * idx + 1] = in.g_mean2d_y; gp.means2D[3 * idx + 2] = 0.f; }
       }
       if (gp.opacities) {
-        if (gp.accumulate) gp.opacities[idx] += g_op; else gp.opacities[idx] = g_op;
+        if (gp.accumulate) red_add(gp.opacities + idx, g_op); else gp.opacities[idx] = g_op;
       }
       // densification statistics of this view (scene/gaussian_model.py:502-506, train.py:313-314)
       if (gp.densify_grad_accum)
-        gp.densify_grad_accum[idx] += sqrtf(in.g_mean2d_x * in.g_mean2d_x + in.g_mean2d_y * in.g_mean2d_y);
-      if (gp.densify_denom) gp.densify_denom[idx] += 1.0f;
-      if (gp.max_radii2D) gp.max_radii2D[idx] = max(gp.max_radii2D[idx], radius);
+        red_add(gp.densify_grad_accum + idx, sqrtf(in.g_mean2d_x * in.g_mean2d_x + in.g_mean2d_y * in.g_mean2d_y));
+      if (gp.densify_denom) red_add(gp.densify_denom + idx, 1.0f);
+      if (gp.max_radii2D) atomicMax(gp.max_radii2D + idx, radius);
     }
     if (want_sh) {
       fence_async_smem();  // generic-proxy writes of sh_out -> visible to the bulk store
@@ -891,7 +902,7 @@ cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const in
     const int64_t ntiles = (a.P + PB_TILE - 1) / PB_TILE;
     if (gp.color_grad_view) {  // SH backward deferred to launch_sh_backward_views: only the accumulator block is staged
       const int bulk_ok = al16(acc);
-      const unsigned blocks = (unsigned)(ntiles < 3 * 148 ? ntiles : 3 * 148);
+      const unsigned blocks = (unsigned)(ntiles < PDGS_PB_DEFER_CTAS * 148 ? ntiles : PDGS_PB_DEFER_CTAS * 148);
       preprocess_backward_sh_kernel<true, false><<<blocks, PB_TILE, offsetof(PbShared, sh_in), s>>>(a, g, radii, acc, gp, bulk_ok);
       return cudaGetLastError();
     }
