@@ -214,7 +214,37 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restr
   for (int i = threadIdx.x; i < npass * RADIX; i += blockDim.x) s_hist[i] = 0;
   __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  int64_t tail0 = 0;  // keys [tail0, n) go through the scalar loop below
+  if (sizeof(KeyT) == 4 && (((uintptr_t)keys) & 15u) == 0) {
+    // u32 keys: four 16-byte loads in flight per thread, and equal digits of neighbouring keys (the tiles of one
+    // Gaussian's rect share their high digit, depth keys share their top byte) merged into one shared-memory atomic
+    const int64_t nvec = n / 4;
+    const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += 4 * stride) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * stride < nvec) v[u] = k4[i0 + u * stride];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (i0 + u * stride >= nvec) break;
+        const uint32_t kk[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+        for (int p = 0; p < npass; ++p) {
+          const int nb = min(RADIX_BITS, end_bit - p * RADIX_BITS);
+          const uint32_t msk = (1u << nb) - 1u;
+          uint32_t d = (kk[0] >> (p * RADIX_BITS)) & msk, run = 1;
+#pragma unroll
+          for (int e = 1; e < 4; ++e) {
+            const uint32_t de = (kk[e] >> (p * RADIX_BITS)) & msk;
+            if (de == d) { ++run; } else { atomicAdd(&s_hist[p * RADIX + d], run); d = de; run = 1; }
+          }
+          atomicAdd(&s_hist[p * RADIX + d], run);
+        }
+      }
+    }
+    tail0 = nvec * 4;
+  }
+  for (int64_t i = tail0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const KeyT k = keys[i];
     for (int p = 0; p < npass; ++p) {
       const int nb = min(RADIX_BITS, end_bit - p * RADIX_BITS);  // the last pass may cover fewer than 8 bits
@@ -412,7 +442,24 @@ __global__ void __launch_bounds__(256) ranges_kernel(const uint32_t* __restrict_
   const int64_t n = (int64_t)ld_relaxed_u32(n_dev);
   if (n > capacity) return;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  // four pairs per thread from one 16-byte load (tkeys is 128-byte aligned inside the binning buffer)
+  const int64_t nvec = ((((uintptr_t)tkeys) & 15u) == 0) ? n / 4 : 0;
+  const uint4* k4 = reinterpret_cast<const uint4*>(tkeys);
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += stride) {
+    const uint4 q = k4[v];
+    const int64_t i0 = 4 * v;
+    const uint32_t t[5] = {i0 > 0 ? tkeys[i0 - 1] : q.x, q.x, q.y, q.z, q.w};
+    if (i0 == 0) ranges[q.x].x = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (t[e + 1] != t[e]) {
+        ranges[t[e]].y = (uint32_t)(i0 + e);
+        ranges[t[e + 1]].x = (uint32_t)(i0 + e);
+      }
+    }
+    if (i0 + 4 == n) ranges[q.w].y = (uint32_t)n;
+  }
+  for (int64_t i = 4 * nvec + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const uint32_t t = tkeys[i];
     if (i == 0) ranges[t].x = 0;
     else {

@@ -671,7 +671,8 @@ __global__ void __launch_bounds__(PB_TILE, DEFER ? PDGS_PB_DEFER_CTAS : 2) prepr
 // accumulators and the direction term to dL/dmean.
 // ------------------------------------------------------------------------------------------
 constexpr int SHV_THREADS = 128;
-constexpr int SHV_MAX_VIEWS = 256;  // camera positions staged per launch (longer batches loop on the host)
+constexpr int SHV_MAX_VIEWS = 256;
+constexpr int SHV_VB = 8;          // views whose colour gradients are in flight per thread  // camera positions staged per launch (longer batches loop on the host)
 
 template <int MT>  // MT = 16: fully unrolled register path; MT = 0: any M through global memory
 __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_kernel(const float* __restrict__ means3D,
@@ -701,20 +702,32 @@ __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_kernel(const fl
 #pragma unroll
     for (int k = 0; k < 48; ++k) acc[k] = 0.f;
     bool any = false;
-    for (int v = 0; v < n_views; ++v) {
-      const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
-      const float g[3] = {__ldg(gsrc), __ldg(gsrc + 1), __ldg(gsrc + 2)};
-      if (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f) continue;  // culled in this view, or no gradient reached it
-      any = true;
-      float gdir[3], basis[16];
-      sh_backward_dir(sh_degree, mx - s_cam[3 * v], my - s_cam[3 * v + 1], mz - s_cam[3 * v + 2], sh, g, gdir, basis);
-      gm[0] += gdir[0]; gm[1] += gdir[1]; gm[2] += gdir[2];
+    // the per-view colour gradients are fetched VB views ahead of their use: one dependent DRAM round trip per view
+    // would otherwise serialise the loop (64 views = 64 round trips per thread)
+    for (int v0 = 0; v0 < n_views; v0 += SHV_VB) {
+      float gb[SHV_VB][3];
 #pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        const float bk = (k < ncoef) ? basis[k] : 0.f;
-        acc[3 * k] = fmaf(bk, g[0], acc[3 * k]);
-        acc[3 * k + 1] = fmaf(bk, g[1], acc[3 * k + 1]);
-        acc[3 * k + 2] = fmaf(bk, g[2], acc[3 * k + 2]);
+      for (int u = 0; u < SHV_VB; ++u) {
+        const int v = (v0 + u < n_views) ? v0 + u : n_views - 1;
+        const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
+        gb[u][0] = __ldg(gsrc); gb[u][1] = __ldg(gsrc + 1); gb[u][2] = __ldg(gsrc + 2);
+      }
+#pragma unroll
+      for (int u = 0; u < SHV_VB; ++u) {
+        const int v = v0 + u;
+        const float g[3] = {gb[u][0], gb[u][1], gb[u][2]};
+        if (v >= n_views || (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f)) continue;  // culled in this view / no gradient
+        any = true;
+        float gdir[3], basis[16];
+        sh_backward_dir(sh_degree, mx - s_cam[3 * v], my - s_cam[3 * v + 1], mz - s_cam[3 * v + 2], sh, g, gdir, basis);
+        gm[0] += gdir[0]; gm[1] += gdir[1]; gm[2] += gdir[2];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float bk = (k < ncoef) ? basis[k] : 0.f;
+          acc[3 * k] = fmaf(bk, g[0], acc[3 * k]);
+          acc[3 * k + 1] = fmaf(bk, g[1], acc[3 * k + 1]);
+          acc[3 * k + 2] = fmaf(bk, g[2], acc[3 * k + 2]);
+        }
       }
     }
     if (grad_shs && (any || !accumulate)) {
@@ -789,19 +802,29 @@ __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_split_kernel(
       float acc[48];
 #pragma unroll
       for (int k = 0; k < 48; ++k) acc[k] = 0.f;
-      for (int v = 0; v < n_views; ++v) {
-        const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
-        const float g[3] = {__ldg(gsrc), __ldg(gsrc + 1), __ldg(gsrc + 2)};
-        if (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f) continue;  // culled in this view, or no gradient reached it
-        float gdir[3], basis[16];
-        sh_backward_dir(sh_degree, mx - s_cam[3 * v], my - s_cam[3 * v + 1], mz - s_cam[3 * v + 2], sh, g, gdir, basis);
-        gm[0] += gdir[0]; gm[1] += gdir[1]; gm[2] += gdir[2];
+      for (int v0 = 0; v0 < n_views; v0 += SHV_VB) {  // colour gradients fetched SHV_VB views ahead, as above
+        float gb[SHV_VB][3];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-          const float bk = (k < ncoef) ? basis[k] : 0.f;
-          acc[3 * k] = fmaf(bk, g[0], acc[3 * k]);
-          acc[3 * k + 1] = fmaf(bk, g[1], acc[3 * k + 1]);
-          acc[3 * k + 2] = fmaf(bk, g[2], acc[3 * k + 2]);
+        for (int u = 0; u < SHV_VB; ++u) {
+          const int v = (v0 + u < n_views) ? v0 + u : n_views - 1;
+          const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
+          gb[u][0] = __ldg(gsrc); gb[u][1] = __ldg(gsrc + 1); gb[u][2] = __ldg(gsrc + 2);
+        }
+#pragma unroll
+        for (int u = 0; u < SHV_VB; ++u) {
+          const int v = v0 + u;
+          const float g[3] = {gb[u][0], gb[u][1], gb[u][2]};
+          if (v >= n_views || (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f)) continue;
+          float gdir[3], basis[16];
+          sh_backward_dir(sh_degree, mx - s_cam[3 * v], my - s_cam[3 * v + 1], mz - s_cam[3 * v + 2], sh, g, gdir, basis);
+          gm[0] += gdir[0]; gm[1] += gdir[1]; gm[2] += gdir[2];
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const float bk = (k < ncoef) ? basis[k] : 0.f;
+            acc[3 * k] = fmaf(bk, g[0], acc[3 * k]);
+            acc[3 * k + 1] = fmaf(bk, g[1], acc[3 * k + 1]);
+            acc[3 * k + 2] = fmaf(bk, g[2], acc[3 * k + 2]);
+          }
         }
       }
 #pragma unroll

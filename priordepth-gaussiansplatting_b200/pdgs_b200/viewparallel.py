@@ -20,8 +20,10 @@ from typing import Callable, Dict, List, Optional, Sequence
 import torch
 import torch.distributed as dist
 
-# segments of the flat gradient buffer: (name, floats per Gaussian); shs uses M*3
-_SEGMENTS = (("means3D", 3), ("shs", None), ("opacities", 1), ("scales", 3), ("rotations", 4),
+# segments of the flat gradient buffer: (name, floats per Gaussian); shs_rest uses (M-1)*3.  The SH gradient occupies
+# the adjacent shs_dc + shs_rest segments: as two tensors for a split scene (features_dc / features_rest), or as ONE
+# packed [P,M,3] tensor ("shs") laid over the start of the same region.
+_SEGMENTS = (("means3D", 3), ("shs_dc", 3), ("shs_rest", None), ("opacities", 1), ("scales", 3), ("rotations", 4),
              ("densify_grad_accum", 1), ("densify_denom", 1))
 
 
@@ -42,9 +44,10 @@ class GradBuffer:
         off = 0
         self._spans: Dict[str, tuple] = {}
         for name, width in _SEGMENTS:
-            w = 3 * self.M if width is None else width
+            w = 3 * (self.M - 1) if width is None else width
             self._spans[name] = (off, self.P * w, w)
             off += (self.P * w + 3) // 4 * 4
+        self._spans["shs"] = (self._spans["shs_dc"][0], self.P * 3 * self.M, 3 * self.M)
         self.flat = torch.zeros(max(off, 4), dtype=torch.float32, device=device)
         self.max_radii2D = torch.zeros(self.P, dtype=torch.int32, device=device)
 
@@ -53,6 +56,10 @@ class GradBuffer:
         t = self.flat[off:off + n]
         if name == "shs":
             return t.view(self.P, self.M, 3)
+        if name == "shs_dc":
+            return t.view(self.P, 1, 3)
+        if name == "shs_rest":
+            return t.view(self.P, max(self.M - 1, 0), 3)
         return t.view(self.P, w) if w > 1 or name == "opacities" else t.view(self.P)
 
     def zero_(self) -> "GradBuffer":
@@ -60,8 +67,13 @@ class GradBuffer:
         self.max_radii2D.zero_()
         return self
 
-    def accumulate_dict(self) -> Dict[str, torch.Tensor]:
-        d = {name: self.view(name) for name, _ in _SEGMENTS}
+    def accumulate_dict(self, split: bool = False) -> Dict[str, torch.Tensor]:
+        """split: the SH gradient as shs_dc / shs_rest (scene given as features_dc / features_rest), else packed `shs`."""
+        d = {name: self.view(name) for name, _ in _SEGMENTS if not name.startswith("shs")}
+        if split:
+            d["shs_dc"], d["shs_rest"] = self.view("shs_dc"), self.view("shs_rest")
+        else:
+            d["shs"] = self.view("shs")
         d["max_radii2D"] = self.max_radii2D
         return d
 
@@ -72,7 +84,7 @@ class GradBuffer:
 
     @property
     def floats_per_gaussian(self) -> int:
-        return sum((3 * self.M if w is None else w) for _, w in _SEGMENTS)
+        return sum((3 * (self.M - 1) if w is None else w) for _, w in _SEGMENTS)
 
 
 def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, mask, w_depth, acc: Dict, loss_acc,
@@ -81,13 +93,16 @@ def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, ma
     the reference's training loss (1-l)*L1 + l*(1-SSIM) (/root/reference/train.py:153-159), else plain L1."""
     from . import rasterizer as rz
     empty = torch.empty(0, device=gaussians["means3D"].device)
-    shs = gaussians.get("shs")
+    # split SH (features_dc / features_rest) and raw parameters: SURVEY 8(f) rank 2, see rz.rasterize_gaussians
+    dc = gaussians.get("shs_dc")
+    shs = gaussians.get("shs_rest") if dc is not None else gaussians.get("shs")
+    raw = bool(gaussians.get("raw_params", False))
     colors = gaussians.get("colors_precomp")
     num_rendered, color, radii, geom, binning, img, invd = rz.rasterize_gaussians(
         rs.bg, gaussians["means3D"], empty if colors is None else colors, gaussians["opacities"], gaussians["scales"],
         gaussians["rotations"], rs.scale_modifier, empty, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
         rs.image_height, rs.image_width, empty if shs is None else shs, rs.sh_degree, rs.campos, False, rs.antialiasing,
-        rs.debug)
+        rs.debug, dc=dc, raw_params=raw)
     launches = rz.LAUNCHES_FORWARD
     use_depth = prior is not None and w_depth != 0.0
     if lambda_dssim > 0.0:
@@ -107,7 +122,7 @@ def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, ma
         rs.bg, gaussians["means3D"], radii, empty if colors is None else colors, gaussians["opacities"],
         gaussians["scales"], gaussians["rotations"], rs.scale_modifier, empty, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
         rs.tanfovy, dcolor, ddepth, empty if shs is None else shs, rs.sh_degree, rs.campos, geom, num_rendered, binning,
-        img, rs.antialiasing, rs.debug, accumulate_into=acc)
+        img, rs.antialiasing, rs.debug, accumulate_into=acc, dc=dc, raw_params=raw)
     launches += rz.LAUNCHES_BACKWARD
     return dict(num_rendered=num_rendered, launches=launches, radii=radii, color=color, invdepth=invd)
 
@@ -163,19 +178,22 @@ class ViewParallelRasterizer:
              priors: Optional[Dict[int, torch.Tensor]] = None, masks: Optional[Dict[int, torch.Tensor]] = None,
              w_depth: float = 0.0, reduce: bool = True, keep_outputs: bool = False, lambda_dssim: float = 0.0) -> Dict:
         """gaussians: means3D/shs/opacities/scales/rotations (post-activation, as render() passes them,
-        /root/reference/gaussian_renderer/__init__.py:57-112); views: one GaussianRasterizationSettings per
+        /root/reference/gaussian_renderer/__init__.py:57-112); optionally `shs_dc` + `shs_rest` instead of `shs`
+        (features_dc / features_rest, gradients then in buf.view("shs_dc") / ("shs_rest")) and `raw_params=True`
+        (opacities / scales / rotations are the pre-activation parameters, gradients w.r.t. them); views: one GaussianRasterizationSettings per
         camera of the WHOLE batch (identical on every rank); targets/priors/masks: dict view index -> tensor
         for at least this rank's shard.  Returns summed-over-views gradients (all ranks) in self.buf."""
         my = shard_views(len(views), self.rank, self.world)
         self.buf.zero_()
         self.loss_acc.zero_()
-        acc = self.buf.accumulate_dict()
+        split = gaussians.get("shs_dc") is not None
+        acc = self.buf.accumulate_dict(split)
         self.last_launches = 0
         self.last_num_rendered = []
         outs = []
         # Deferred SH backward (CUDA backend, SH colours): every view leaves only its masked dL/drgb [P,3]; the SH
         # coefficients are read and their gradient written once per batch by pdgs_sh_backward_views.
-        defer = self.backend is _cuda_view_backend and gaussians.get("shs") is not None and len(my) > 0
+        defer = self.backend is _cuda_view_backend and (split or gaussians.get("shs") is not None) and len(my) > 0
         if defer:
             need = (len(my), self.buf.P, 3)
             if self._color_grads is None or tuple(self._color_grads.shape) != need:
@@ -201,8 +219,13 @@ class ViewParallelRasterizer:
         if defer:
             from . import rasterizer as rz
             campos = torch.stack([views[i].campos.reshape(3) for i in my]).to(self.device, torch.float32)
-            rz.sh_backward_views(gaussians["means3D"], gaussians["shs"], views[my[0]].sh_degree, campos,
-                                 self._color_grads, acc["shs"], acc["means3D"], accumulate=True)
+            if split:
+                rz.sh_backward_views_split(gaussians["means3D"], gaussians["shs_dc"], gaussians.get("shs_rest"),
+                                           views[my[0]].sh_degree, campos, self._color_grads, acc["shs_dc"],
+                                           acc["shs_rest"], acc["means3D"], accumulate=True)
+            else:
+                rz.sh_backward_views(gaussians["means3D"], gaussians["shs"], views[my[0]].sh_degree, campos,
+                                     self._color_grads, acc["shs"], acc["means3D"], accumulate=True)
             self.last_launches += rz.LAUNCHES_SH_BWD
         if reduce and self.world > 1:
             self.buf.all_reduce(self.group)

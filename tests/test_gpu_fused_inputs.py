@@ -147,3 +147,31 @@ def test_split_degree0_model_and_errors():
         GaussianRasterizer(rs)(means3D=lv["means3D"], means2D=lv["means2D"], opacities=lv["opacities"],
                                scales=lv["scales"], rotations=lv["rotations"], dc=dc,
                                colors_precomp=torch.rand(sc.P, 3, device=DEV), shs=lv["shs"][:, 1:, :])
+
+
+def test_batch_step_split_raw_equals_sum_of_single_view_autograd():
+    """The view-parallel batch step fed with features_dc / features_rest and raw parameters accumulates the same
+    gradients as per-view autograd through the fused drop-in call."""
+    from pdgs_b200.viewparallel import ViewParallelRasterizer
+    sc = scenes.make_config("C4", P=6000, n_views=3, scale_image=0.1)
+    H, W = sc.views[0].image_height, sc.views[0].image_width
+    rp = raw_params(sc)
+    gen = torch.Generator().manual_seed(4)
+    targets = {i: torch.rand(3, H, W, generator=gen).to(DEV) for i in range(3)}
+    sums = None
+    for i, view in enumerate(sc.views):
+        lv = leaves(rp, DEV)
+        color, radii, invd = run_fused(sc, view, lv, split=True, raw=True)
+        (color - targets[i]).abs().mean().backward()
+        g = {k: lv[k].grad for k in ("means3D", "_opacity", "_scaling", "_rotation", "dc", "rest")}
+        sums = g if sums is None else {k: sums[k] + g[k] for k in g}
+    vp = ViewParallelRasterizer(sc.P, 16, DEV)
+    gaussians = dict(means3D=rp["means3D"].to(DEV), opacities=rp["_opacity"].to(DEV), scales=rp["_scaling"].to(DEV),
+                     rotations=rp["_rotation"].to(DEV), shs_dc=rp["dc"].to(DEV), shs_rest=rp["rest"].to(DEV),
+                     raw_params=True)
+    views = [helpers.cuda_settings(sc, v, DEV) for v in sc.views]
+    vp.step(gaussians, views, targets)
+    names = dict(means3D="means3D", _opacity="opacities", _scaling="scales", _rotation="rotations", dc="shs_dc", rest="shs_rest")
+    for k, seg in names.items():
+        e = helpers.rel_err(vp.buf.view(seg), sums[k].view_as(vp.buf.view(seg)))
+        assert e < 2e-5, (k, e)

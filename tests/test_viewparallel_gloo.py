@@ -37,6 +37,15 @@ def test_grad_buffer_layout():
         assert float(b.flat.sum()) == 61 * P  # segments are disjoint and cover 61 floats per Gaussian
         assert b.view("shs").shape == (P, 16, 3) and b.view("means3D").shape == (P, 3)
         assert b.view("opacities").shape == (P, 1) and b.view("densify_denom").shape == (P,)
+        # split layout (features_dc / features_rest): same 61 floats, both tensors 16-byte aligned and disjoint
+        b2 = GradBuffer(P, 16, "cpu")
+        d2 = b2.accumulate_dict(split=True)
+        assert "shs" not in d2 and d2["shs_dc"].shape == (P, 1, 3) and d2["shs_rest"].shape == (P, 15, 3)
+        for name, t in d2.items():
+            if name != "max_radii2D":
+                assert t.data_ptr() % 16 == 0, name
+                t += 1.0
+        assert float(b2.flat.sum()) == 61 * P
 
 
 def _oracle_backend(scene):
