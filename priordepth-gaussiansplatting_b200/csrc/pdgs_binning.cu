@@ -276,7 +276,7 @@ __device__ __forceinline__ unsigned warp_peers(uint32_t d, int nbits) {
 }
 
 template <typename KeyT, int ITEMS>
-__global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? 4 : 3) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
+__global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? (ITEMS <= 8 ? 6 : 4) : 3) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     KeyT* __restrict__ keys_out,
                                                                     uint32_t* __restrict__ vals_out, const uint32_t* n_dev,

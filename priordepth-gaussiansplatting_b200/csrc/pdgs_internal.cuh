@@ -15,7 +15,10 @@ constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
 constexpr int MAX_PASSES = 8;
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS_U32 = 16;  // 4096 pairs per CTA (u32 keys: depth bits, tile ids)
+#ifndef PDGS_SORT_ITEMS
+#define PDGS_SORT_ITEMS 16
+#endif
+constexpr int SORT_ITEMS_U32 = PDGS_SORT_ITEMS;  // pairs per thread, 256 threads per CTA (u32 keys: depth bits, tile ids)
 constexpr int SORT_ITEMS_U64 = 12;  // 3072 pairs per CTA (u64 keys: stand-alone pdgs_sort_pairs)
 constexpr int DEPTH_SORT_PASSES = 4;
 constexpr int SCAN_THREADS = 256;
