@@ -142,6 +142,7 @@ class ViewParallelRasterizer:
         self.last_launches = 0
         self.last_num_rendered: List[int] = []
         self._copy_stream = None
+        self._param_stream = None
         self._color_grads = None
 
     def _upload(self, i, targets, priors, masks):
@@ -155,6 +156,44 @@ class ViewParallelRasterizer:
             ev = torch.cuda.Event()
             ev.record(self._copy_stream)
         return items, ev
+
+    def stage_gaussians(self, host: Dict[str, torch.Tensor]):
+        """Start copying a dict of (pinned) host tensors -- the Gaussian parameters of an upcoming step -- to the device on
+        the copy stream and return a handle for step(gaussians=handle).  Called before the loss of the current step
+        is read back, it lets the next step's 236 B/Gaussian upload overlap this step's kernels."""
+        if self.device.type != "cuda":
+            return dict(host), None
+        if self._param_stream is None:  # its own stream: the per-view image uploads must not queue behind it
+            self._param_stream = torch.cuda.Stream(self.device)
+        with torch.cuda.stream(self._param_stream):
+            g = {k: (v.to(self.device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in host.items()}
+            ev = torch.cuda.Event()
+            ev.record(self._param_stream)
+        return g, ev
+
+    def _prefetch_begin(self, host: Dict[str, torch.Tensor]):
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(self.device)
+        with torch.cuda.stream(self._copy_stream):  # allocated on the stream that fills them
+            dev = {k: (torch.empty(v.shape, dtype=v.dtype, device=self.device) if torch.is_tensor(v) else v)
+                   for k, v in host.items()}
+        return host, dev
+
+    def _prefetch_slice(self, nxt, k: int, n: int) -> None:
+        host, dev = nxt
+        with torch.cuda.stream(self._copy_stream):
+            for name, src in host.items():
+                if not torch.is_tensor(src):
+                    continue
+                s, d = src.reshape(-1), dev[name].view(-1)
+                a, b = s.numel() * k // n, s.numel() * (k + 1) // n
+                if b > a:
+                    d[a:b].copy_(s[a:b], non_blocking=True)
+
+    def _prefetch_end(self, nxt):
+        ev = torch.cuda.Event()
+        ev.record(self._copy_stream)
+        return nxt[1], ev
 
     def _await(self, staged):
         items, ev = staged
@@ -176,13 +215,27 @@ class ViewParallelRasterizer:
 
     def step(self, gaussians: Dict[str, torch.Tensor], views: Sequence, targets: Dict[int, torch.Tensor],
              priors: Optional[Dict[int, torch.Tensor]] = None, masks: Optional[Dict[int, torch.Tensor]] = None,
-             w_depth: float = 0.0, reduce: bool = True, keep_outputs: bool = False, lambda_dssim: float = 0.0) -> Dict:
+             w_depth: float = 0.0, reduce: bool = True, keep_outputs: bool = False, lambda_dssim: float = 0.0,
+             prefetch_gaussians: Optional[Dict[str, torch.Tensor]] = None) -> Dict:
         """gaussians: means3D/shs/opacities/scales/rotations (post-activation, as render() passes them,
         /root/reference/gaussian_renderer/__init__.py:57-112); optionally `shs_dc` + `shs_rest` instead of `shs`
         (features_dc / features_rest, gradients then in buf.view("shs_dc") / ("shs_rest")) and `raw_params=True`
         (opacities / scales / rotations are the pre-activation parameters, gradients w.r.t. them); views: one GaussianRasterizationSettings per
         camera of the WHOLE batch (identical on every rank); targets/priors/masks: dict view index -> tensor
-        for at least this rank's shard.  Returns summed-over-views gradients (all ranks) in self.buf."""
+        for at least this rank's shard.  Returns summed-over-views gradients (all ranks) in self.buf.
+
+        prefetch_gaussians: pinned HOST tensors of the NEXT step's Gaussians.  They are uploaded during this step, one
+        slice per view, on the same copy stream and behind that view's image upload (host->device copies of different
+        streams share one DMA queue, so a single 236 B/Gaussian copy issued up front would hold the images back and
+        stall the kernels); the handle comes back as out["prefetched"] and is passed as `gaussians` to the next step."""
+        if isinstance(gaussians, tuple):  # handle from stage_gaussians(): wait for the upload on the compute stream
+            gaussians, ev = gaussians
+            if ev is not None:
+                cur = torch.cuda.current_stream(self.device)
+                cur.wait_event(ev)
+                for t in gaussians.values():
+                    if torch.is_tensor(t):
+                        t.record_stream(cur)
         my = shard_views(len(views), self.rank, self.world)
         self.buf.zero_()
         self.loss_acc.zero_()
@@ -201,9 +254,12 @@ class ViewParallelRasterizer:
         # Per-view images (target / prior / mask) may live in pinned HOST memory: they are uploaded on a side
         # stream one view ahead of the rasterizer, so the host->device copies overlap the kernels.
         pending = self._upload(my[0], targets, priors, masks) if len(my) else None
+        nxt = self._prefetch_begin(prefetch_gaussians) if prefetch_gaussians is not None else None
         for k, i in enumerate(my):
             cur = pending
             pending = self._upload(my[k + 1], targets, priors, masks) if k + 1 < len(my) else None
+            if nxt is not None:
+                self._prefetch_slice(nxt, k, len(my))
             tgt, pri, msk = self._await(cur)
             if defer:
                 acc["color_grad_view"] = self._color_grads[k]
@@ -230,4 +286,9 @@ class ViewParallelRasterizer:
         if reduce and self.world > 1:
             self.buf.all_reduce(self.group)
             dist.all_reduce(self.loss_acc, op=dist.ReduceOp.SUM, group=self.group)
-        return dict(loss_sums=self.loss_acc, grads=self.buf, local_views=list(my), outputs=outs)
+        prefetched = None
+        if nxt is not None:
+            if len(my) == 0:
+                self._prefetch_slice(nxt, 0, 1)
+            prefetched = self._prefetch_end(nxt)
+        return dict(loss_sums=self.loss_acc, grads=self.buf, local_views=list(my), outputs=outs, prefetched=prefetched)

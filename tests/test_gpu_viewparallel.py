@@ -116,3 +116,26 @@ def test_batch_step_with_ssim_training_loss_equals_autograd_through_the_dropin_p
     for k in sums:
         assert helpers.rel_err(vp.buf.view(k), sums[k].view_as(vp.buf.view(k))) < 5e-5, k
     assert abs(float(vp.loss_acc[2]) - ssim_sum) < 1e-4
+
+
+def test_step_from_staged_host_gaussians():
+    """step(gaussians=stage_gaussians(host)) -- parameters uploaded on the side stream, images from pinned host memory --
+    gives the same gradients as the all-resident step."""
+    from pdgs_b200.viewparallel import ViewParallelRasterizer
+    sc = scenes.make_config("C4", P=5000, n_views=3, scale_image=0.1)
+    H, W = sc.views[0].image_height, sc.views[0].image_width
+    gen = torch.Generator().manual_seed(9)
+    tg_host = {i: torch.rand(3, H, W, generator=gen).pin_memory() for i in range(3)}
+    host = {k: getattr(sc, k).contiguous().pin_memory() for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    views = [helpers.cuda_settings(sc, v, DEV) for v in sc.views]
+    a = ViewParallelRasterizer(sc.P, 16, DEV)
+    a.step({k: v.to(DEV) for k, v in host.items()}, views, {i: t.to(DEV) for i, t in tg_host.items()})
+    b = ViewParallelRasterizer(sc.P, 16, DEV)
+    handle = b.stage_gaussians(host)
+    nxt = b.stage_gaussians(host)  # a second upload in flight, as the pipelined loop does
+    out = b.step(handle, views, tg_host, prefetch_gaussians=host)   # next step's parameters uploaded slice by slice
+    b.step(nxt, views, tg_host)
+    b.step(out["prefetched"], views, tg_host)
+    torch.cuda.synchronize()
+    assert helpers.rel_err(b.buf.flat, a.buf.flat) < 2e-5
+    assert torch.equal(b.buf.max_radii2D, a.buf.max_radii2D)
