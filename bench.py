@@ -245,7 +245,6 @@ def main():
     for _ in range(args.warmup):
         vp.step(g_dev, views_dev, tgt_dev)
     barrier()
-    rz.set_stage_timing(dev, True)
     sampler, sampler_path = start_clock_sampler(local_rank) if rank == 0 else (None, None)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches, pairs = 0, []
@@ -259,8 +258,25 @@ def main():
     barrier()
     clocks = stop_clock_sampler(sampler, sampler_path) if rank == 0 else None
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    # Per-stage durations (roofline / stages): a second measured region of the same steps with ONE view in flight.  In
+    # the region above `lanes` views run concurrently on separate streams, so a stage's event pair would also cover
+    # kernels of other views; one view at a time gives each kernel's own duration (the figure ncu's launch list shows).
+    lanes = vp.lanes
+    vp.lanes = 1
+    vp.step(g_dev, views_dev, tgt_dev)
+    barrier()
+    rz.set_stage_timing(dev, True)
+    rz.stage_times(dev)
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for _ in range(args.steps):
+        vp.step(g_dev, views_dev, tgt_dev)
+    s1.record()
+    barrier()
     stage = rz.stage_times(dev)
     rz.set_stage_timing(dev, False)
+    ms_one_lane = s0.elapsed_time(s1) / args.steps
+    vp.lanes = lanes
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         lt = torch.tensor([launches], dtype=torch.int64, device=dev)
@@ -404,6 +420,9 @@ def main():
                 higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
                 config=workload_config(args, scene, world), clocks=clocks, e2e=e2e, gpu_launches=launches,
                 roofline=roofline, stages=stages, cpu_baseline=cpu_baseline,
+                stage_timing=dict(lanes=1, ms_per_step=ms_one_lane,
+                                  note="stages / roofline come from a second measured region of the same steps with one view "
+                                       "in flight; `value` is measured with config.lanes views in flight on separate streams"),
                 work_per_view=dict(P=Pn, visible=V, pairs=R, n_test=work["n_test"] / nv, n_acc=work["n_acc"] / nv,
                                    n_test_bwd=work["n_test_bwd"] / nv),
                 loss_mean=loss_mean)
@@ -419,6 +438,7 @@ def workload_config(args, scene, world):
                          f"fwd + L1 loss + bwd per view, grads summed over views",
                 gaussians=scene.P, views_per_step=len(scene.views), image=[v.image_width, v.image_height],
                 parallelism=f"view-parallel x{world} (Gaussians replicated, one all-reduce of [P,61] fp32 per step)",
+                lanes=int(os.environ.get("PDGS_LANES", "3")),
                 l2_policy="inputs larger than L2 (708 MB of Gaussian parameters streamed per view vs 126 MB L2); no flush")
 
 

@@ -10,6 +10,17 @@ namespace {
 
 constexpr int PRE_THREADS = 256;
 
+// Accumulation into the per-Gaussian gradient rows (batch path) uses fire-and-forget reductions: the add happens in
+// L2 and the thread never waits for the old value (a load-add-store would put one more DRAM round trip at the end of
+// every thread of this latency-bound kernel).  Atomic, so several views' backward kernels may run concurrently on
+// different streams and add into the same rows (ViewParallelRasterizer lanes).
+__device__ __forceinline__ void red_add(float* p, float v) {
+  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_add4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 __device__ __forceinline__ void load_camera(const DeviceArgs& a, Camera* cam) {
   // one CTA-wide cooperative load of the 35 camera floats into shared memory
   const int t = threadIdx.x;
@@ -254,7 +265,8 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
   if (a.colors_precomp) {
     if (gp.colors_precomp) {
       if (gp.accumulate) {
-        gp.colors_precomp[3 * idx] += in.g_rgb[0]; gp.colors_precomp[3 * idx + 1] += in.g_rgb[1]; gp.colors_precomp[3 * idx + 2] += in.g_rgb[2];
+        red_add(gp.colors_precomp + 3 * idx, in.g_rgb[0]); red_add(gp.colors_precomp + 3 * idx + 1, in.g_rgb[1]);
+        red_add(gp.colors_precomp + 3 * idx + 2, in.g_rgb[2]);
       } else {
         gp.colors_precomp[3 * idx] = in.g_rgb[0]; gp.colors_precomp[3 * idx + 1] = in.g_rgb[1]; gp.colors_precomp[3 * idx + 2] = in.g_rgb[2];
       }
@@ -292,8 +304,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
 #pragma unroll
         for (int k = 0; k < 12; ++k) {
           float4 v = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
-          if (gp.accumulate) { const float4 o = dst[k]; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
-          dst[k] = v;
+          if (gp.accumulate) red_add4(reinterpret_cast<float*>(dst + k), v.x, v.y, v.z, v.w); else dst[k] = v;
         }
       } else {
         float* dst = gp.shs + (size_t)idx * 3 * M;
@@ -301,7 +312,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
           const float bk = (k < n) ? basis[k] : 0.f;
           for (int c = 0; c < 3; ++c) {
             const float v = bk * grgb[c];
-            if (gp.accumulate) dst[3 * k + c] += v; else dst[3 * k + c] = v;
+            if (gp.accumulate) red_add(dst + 3 * k + c, v); else dst[3 * k + c] = v;
           }
         }
       }
@@ -312,7 +323,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
     if (gp.cov3D_precomp) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
-        if (gp.accumulate) gp.cov3D_precomp[6 * idx + k] += g_cov[k]; else gp.cov3D_precomp[6 * idx + k] = g_cov[k];
+        if (gp.accumulate) red_add(gp.cov3D_precomp + 6 * idx + k, g_cov[k]); else gp.cov3D_precomp[6 * idx + k] = g_cov[k];
       }
     }
   } else {
@@ -322,34 +333,32 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
     if (gp.scales) {
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
-        if (gp.accumulate) gp.scales[3 * idx + k] += g_scale[k]; else gp.scales[3 * idx + k] = g_scale[k];
+        if (gp.accumulate) red_add(gp.scales + 3 * idx + k, g_scale[k]); else gp.scales[3 * idx + k] = g_scale[k];
       }
     }
     if (gp.rotations) {
-      float4* dst = reinterpret_cast<float4*>(gp.rotations) + idx;
-      float4 v = make_float4(g_rot[0], g_rot[1], g_rot[2], g_rot[3]);
-      if (gp.accumulate) { const float4 o = *dst; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
-      *dst = v;
+      if (gp.accumulate) red_add4(gp.rotations + 4 * idx, g_rot[0], g_rot[1], g_rot[2], g_rot[3]);
+      else reinterpret_cast<float4*>(gp.rotations)[idx] = make_float4(g_rot[0], g_rot[1], g_rot[2], g_rot[3]);
     }
   }
   if (gp.means3D) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-      if (gp.accumulate) gp.means3D[3 * idx + k] += g_mean[k]; else gp.means3D[3 * idx + k] = g_mean[k];
+      if (gp.accumulate) red_add(gp.means3D + 3 * idx + k, g_mean[k]); else gp.means3D[3 * idx + k] = g_mean[k];
     }
   }
   if (gp.means2D) {
-    if (gp.accumulate) { gp.means2D[3 * idx] += in.g_mean2d_x; gp.means2D[3 * idx + 1] += in.g_mean2d_y; }
+    if (gp.accumulate) { red_add(gp.means2D + 3 * idx, in.g_mean2d_x); red_add(gp.means2D + 3 * idx + 1, in.g_mean2d_y); }
     else { gp.means2D[3 * idx] = in.g_mean2d_x; gp.means2D[3 * idx + 1] = in.g_mean2d_y; gp.means2D[3 * idx + 2] = 0.f; }
   }
   if (gp.opacities) {
-    if (gp.accumulate) gp.opacities[idx] += g_op; else gp.opacities[idx] = g_op;
+    if (gp.accumulate) red_add(gp.opacities + idx, g_op); else gp.opacities[idx] = g_op;
   }
   // densification statistics of this view (scene/gaussian_model.py:502-506, train.py:313-314)
   if (gp.densify_grad_accum)
-    gp.densify_grad_accum[idx] += sqrtf(in.g_mean2d_x * in.g_mean2d_x + in.g_mean2d_y * in.g_mean2d_y);
-  if (gp.densify_denom) gp.densify_denom[idx] += 1.0f;
-  if (gp.max_radii2D) gp.max_radii2D[idx] = max(gp.max_radii2D[idx], radii[idx]);
+    red_add(gp.densify_grad_accum + idx, sqrtf(in.g_mean2d_x * in.g_mean2d_x + in.g_mean2d_y * in.g_mean2d_y));
+  if (gp.densify_denom) red_add(gp.densify_denom + idx, 1.0f);
+  if (gp.max_radii2D) atomicMax(gp.max_radii2D + idx, radii[idx]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -364,16 +373,6 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
 // occupies the SM.  Two CTAs share an SM: one computes while the other's copies are in flight.
 // ------------------------------------------------------------------------------------------
 constexpr int PB_TILE = 256;
-
-// Accumulation into the per-Gaussian gradient rows (batch path) uses fire-and-forget reductions: the add happens in
-// L2 and the thread never waits for the old value (a load-add-store would put one more DRAM round trip at the end of
-// every thread of this latency-bound kernel).  Each row has one writer per launch, so the result is deterministic.
-__device__ __forceinline__ void red_add(float* p, float v) {
-  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
-}
-__device__ __forceinline__ void red_add4(float* p, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
-}
 
 struct PbShared {  // the deferred-SH variant allocates only the part before sh_in
   float acc_in[PB_TILE * ACC_FLOATS];
@@ -398,6 +397,7 @@ struct ShRowSplit {  // split SH row in shared memory: 3 DC floats + 3(M-1) rest
 // SPLIT: the scene holds features_dc [P,3] and features_rest [P,3(M-1)] instead of one [P,3M] array.  The staging
 // regions sh_in / sh_out then hold the tile's rest block ([256][3(M-1)]) followed by its DC block ([256][3]) -- the
 // same 256*3M floats -- each moved by its own bulk copy.
+
 #ifndef PDGS_PB_DEFER_CTAS
 #define PDGS_PB_DEFER_CTAS 3
 #endif
@@ -636,10 +636,10 @@ __global__ void __launch_bounds__(PB_TILE, DEFER ? PDGS_PB_DEFER_CTAS : 2) prepr
           }
         } else {
           for (int i = tid; i < n * rrow; i += PB_TILE) {
-            if (gp.accumulate) dst_rest[i] += sm.sh_out[i]; else dst_rest[i] = sm.sh_out[i];
+            if (gp.accumulate) red_add(dst_rest + i, sm.sh_out[i]); else dst_rest[i] = sm.sh_out[i];
           }
           for (int i = tid; i < n * 3; i += PB_TILE) {
-            if (gp.accumulate) dst_dc[i] += dc_out[i]; else dst_dc[i] = dc_out[i];
+            if (gp.accumulate) red_add(dst_dc + i, dc_out[i]); else dst_dc[i] = dc_out[i];
           }
         }
       } else {
@@ -652,7 +652,7 @@ __global__ void __launch_bounds__(PB_TILE, DEFER ? PDGS_PB_DEFER_CTAS : 2) prepr
         }
       } else {
         for (int i = tid; i < n * row; i += PB_TILE) {
-          if (gp.accumulate) dst[i] += sm.sh_out[i]; else dst[i] = sm.sh_out[i];
+          if (gp.accumulate) red_add(dst + i, sm.sh_out[i]); else dst[i] = sm.sh_out[i];
         }
       }
       }
