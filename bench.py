@@ -124,7 +124,56 @@ def cpu_arm(args, scene, steps, warmup):
 
 
 # --------------------------------------------------------------------------------------------
+class _NvmlSampler:
+    """SM clock + throttle reasons every 5 ms from a host thread (NVML): the timed region of a multi-GPU run lasts tens
+    of milliseconds, far less than one `nvidia-smi -lms` period."""
+
+    def __init__(self, gpu_index):
+        import threading
+        import pynvml
+        self.nv = pynvml
+        pynvml.nvmlInit()
+        h = None
+        try:
+            pr = torch.cuda.get_device_properties(gpu_index)
+            bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        self.h = h
+        self.sm, self.reasons, self.stop = [], 0, False
+        self.max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def _run(self):
+        nv = self.nv
+        while not self.stop:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.reasons |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def finish(self):
+        self.stop = True
+        self.t.join(timeout=2)
+        nv = self.nv
+        names = [("hw_slowdown", nv.nvmlClocksThrottleReasonHwSlowdown),
+                 ("hw_thermal_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown),
+                 ("sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwThermalSlowdown),
+                 ("sw_power_cap", nv.nvmlClocksThrottleReasonSwPowerCap)]
+        sm = sorted(self.sm)
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=self.max,
+                    reasons=sorted(n for n, bit in names if self.reasons & bit), samples=len(sm), source="nvml, 5 ms period")
+
+
 def start_clock_sampler(gpu_index):
+    try:
+        return _NvmlSampler(gpu_index), None
+    except Exception:
+        pass
     f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
     q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -137,6 +186,8 @@ def start_clock_sampler(gpu_index):
 
 
 def stop_clock_sampler(proc, path):
+    if isinstance(proc, _NvmlSampler):
+        return proc.finish()
     out = dict(sm_mhz=None, sm_max_mhz=None, reasons=[], samples=0)
     if proc is not None:
         proc.terminate()
@@ -380,9 +431,8 @@ def main():
         # batch path: SH backward deferred -> per view K9 reads radii 4P, params 44V, moments 48V, records 48V, writes the
         # masked colour gradient 12P and read-modify-writes means/opacity/scales/rotations/densify (52V each way)
         "preprocess_bwd": ("hbm", 16 * Pn + 244 * V),
-        # once per step: means 12, SH 192, V_local colour gradients 12 each, SH gradient 192 (+192 read when accumulating),
-        # means gradient 24
-        "sh_bwd": ("hbm", Pn * (12 + 192 + 12 * max(work["views"], 1) + 384 + 24)),
+        # once per step: means 12, SH 192, V_local colour gradients 12 each, SH gradient 192 written, means gradient 24
+        "sh_bwd": ("hbm", Pn * (12 + 192 + 12 * max(work["views"], 1) + 192 + 24)),
         "loss": ("hbm", 36 * HW),
     }
     traffic = {}

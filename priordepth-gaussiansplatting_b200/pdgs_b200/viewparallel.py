@@ -63,8 +63,15 @@ class GradBuffer:
             return t.view(self.P, max(self.M - 1, 0), 3)
         return t.view(self.P, w) if w > 1 or name == "opacities" else t.view(self.P)
 
-    def zero_(self) -> "GradBuffer":
-        self.flat.zero_()
+    def zero_(self, skip_sh: bool = False) -> "GradBuffer":
+        """skip_sh: leave the SH gradient region alone (the deferred SH backward overwrites every row of it)."""
+        if skip_sh and self.P > 0:
+            a = self._spans["shs_dc"][0]
+            b = self._spans["shs_rest"][0] + (self._spans["shs_rest"][1] + 3) // 4 * 4
+            self.flat[:a].zero_()
+            self.flat[b:].zero_()
+        else:
+            self.flat.zero_()
         self.max_radii2D.zero_()
         return self
 
@@ -242,16 +249,16 @@ class ViewParallelRasterizer:
                     if torch.is_tensor(t):
                         t.record_stream(cur)
         my = shard_views(len(views), self.rank, self.world)
-        self.buf.zero_()
-        self.loss_acc.zero_()
         split = gaussians.get("shs_dc") is not None
+        defer = self.backend is _cuda_view_backend and (split or gaussians.get("shs") is not None) and len(my) > 0
+        self.buf.zero_(skip_sh=defer)  # with the deferred SH backward every SH gradient row is written, not added to
+        self.loss_acc.zero_()
         acc = self.buf.accumulate_dict(split)
         self.last_launches = 0
         self.last_num_rendered = []
         outs = []
         # Deferred SH backward (CUDA backend, SH colours): every view leaves only its masked dL/drgb [P,3]; the SH
         # coefficients are read and their gradient written once per batch by pdgs_sh_backward_views.
-        defer = self.backend is _cuda_view_backend and (split or gaussians.get("shs") is not None) and len(my) > 0
         if defer:
             need = (len(my), self.buf.P, 3)
             if self._color_grads is None or tuple(self._color_grads.shape) != need:
@@ -326,10 +333,10 @@ class ViewParallelRasterizer:
             if split:
                 rz.sh_backward_views_split(gaussians["means3D"], gaussians["shs_dc"], gaussians.get("shs_rest"),
                                            views[my[0]].sh_degree, campos, self._color_grads, acc["shs_dc"],
-                                           acc["shs_rest"], acc["means3D"], accumulate=True)
+                                           acc["shs_rest"], acc["means3D"], accumulate=False)
             else:
                 rz.sh_backward_views(gaussians["means3D"], gaussians["shs"], views[my[0]].sh_degree, campos,
-                                     self._color_grads, acc["shs"], acc["means3D"], accumulate=True)
+                                     self._color_grads, acc["shs"], acc["means3D"], accumulate=False)
             self.last_launches += rz.LAUNCHES_SH_BWD
         if reduce and self.world > 1:
             self.buf.all_reduce(self.group)
