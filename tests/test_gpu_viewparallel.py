@@ -65,14 +65,14 @@ def test_batch_step_equals_sum_of_single_view_autograd():
     out = vp.step(gaussians, views, targets, priors, masks, w_depth)
     assert out["local_views"] == [0, 1, 2, 3] and vp.last_launches > 0
     for k in sums:
-        assert helpers.rel_err(vp.buf.view(k), sums[k].view_as(vp.buf.view(k))) < 2e-5, k
-    assert helpers.rel_err(vp.buf.view("densify_grad_accum"), accum) < 2e-5
+        assert helpers.rel_err(vp.buf.view(k), sums[k].view_as(vp.buf.view(k))) < 1e-4, k
+    assert helpers.rel_err(vp.buf.view("densify_grad_accum"), accum) < 1e-4
     assert torch.equal(vp.buf.view("densify_denom"), denom)
     assert torch.equal(vp.buf.max_radii2D, maxr)
     assert abs(float(vp.loss_acc[0]) - loss) < 1e-5
     # a second step starts from zero again
     vp.step(gaussians, views, targets, priors, masks, w_depth)
-    assert helpers.rel_err(vp.buf.view("shs"), sums["shs"]) < 2e-5
+    assert helpers.rel_err(vp.buf.view("shs"), sums["shs"]) < 1e-4
 
 
 def test_stage_timing_accumulates_without_sync():
@@ -114,7 +114,7 @@ def test_batch_step_with_ssim_training_loss_equals_autograd_through_the_dropin_p
     views = [helpers.cuda_settings(sc, v, DEV) for v in sc.views]
     vp.step(gaussians, views, targets, priors, None, w_depth, lambda_dssim=lam)
     for k in sums:
-        assert helpers.rel_err(vp.buf.view(k), sums[k].view_as(vp.buf.view(k))) < 5e-5, k
+        assert helpers.rel_err(vp.buf.view(k), sums[k].view_as(vp.buf.view(k))) < 1e-4, k
     assert abs(float(vp.loss_acc[2]) - ssim_sum) < 1e-4
 
 
@@ -137,5 +137,34 @@ def test_step_from_staged_host_gaussians():
     b.step(nxt, views, tg_host)
     b.step(out["prefetched"], views, tg_host)
     torch.cuda.synchronize()
-    assert helpers.rel_err(b.buf.flat, a.buf.flat) < 2e-5
+    assert helpers.rel_err(b.buf.flat, a.buf.flat) < 1e-4
     assert torch.equal(b.buf.max_radii2D, a.buf.max_radii2D)
+
+
+@pytest.mark.parametrize("split_raw", [False, True])
+def test_lanes_match_one_view_at_a_time(split_raw):
+    """Three views in flight on separate streams / host threads, all adding into the same buffers with reductions,
+    give the gradients, statistics and losses of the one-view-at-a-time step (up to the order of the fp32 sums)."""
+    from pdgs_b200.viewparallel import ViewParallelRasterizer
+    sc = scenes.make_config("C4", P=9000, n_views=7, scale_image=0.1)
+    H, W = sc.views[0].image_height, sc.views[0].image_width
+    gen = torch.Generator().manual_seed(11)
+    targets = {i: torch.rand(3, H, W, generator=gen).pin_memory() for i in range(7)}   # host images: upload path too
+    priors = {i: torch.rand(1, H, W, generator=gen).to(DEV) for i in range(7)}
+    g = {k: getattr(sc, k).to(DEV) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    if split_raw:
+        g = dict(means3D=g["means3D"], opacities=torch.logit(g["opacities"].clamp(1e-6, 1 - 1e-6)), scales=torch.log(g["scales"]),
+                 rotations=g["rotations"] * 1.3, shs_dc=g["shs"][:, :1].contiguous(), shs_rest=g["shs"][:, 1:].contiguous(),
+                 raw_params=True)
+    views = [helpers.cuda_settings(sc, v, DEV) for v in sc.views]
+    a = ViewParallelRasterizer(sc.P, 16, DEV, lanes=1)
+    b = ViewParallelRasterizer(sc.P, 16, DEV, lanes=3)
+    for lam in (0.0, 0.2):
+        a.step(g, views, targets, priors, None, 0.5, lambda_dssim=lam)
+        out = b.step(g, views, targets, priors, None, 0.5, lambda_dssim=lam)
+        torch.cuda.synchronize()
+        assert out["local_views"] == list(range(7)) and len(b.last_num_rendered) == 7
+        assert b.last_num_rendered == a.last_num_rendered
+        assert helpers.rel_err(b.buf.flat, a.buf.flat) < 1e-4
+        assert torch.equal(b.buf.max_radii2D, a.buf.max_radii2D)
+        assert torch.allclose(b.loss_acc, a.loss_acc, rtol=1e-5, atol=1e-7)
