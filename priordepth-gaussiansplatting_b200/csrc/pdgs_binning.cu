@@ -5,6 +5,8 @@
 //
 // All kernels read the pair count R from device memory (Ctrl::num_rendered) and are guarded by
 // the binning capacity, so the host can enqueue them before it knows R (no mid-forward bubble).
+#include <cstdlib>
+
 #include "pdgs_internal.cuh"
 
 namespace pdgs {
@@ -282,7 +284,7 @@ __global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? (ITEMS <= 
                                                                     uint32_t* __restrict__ vals_out, const uint32_t* n_dev,
                                                                     int64_t n_host, int64_t capacity, int shift,
                                                                     uint32_t digit_mask, const uint32_t* __restrict__ hist,
-                                                                    uint32_t* ticket, uint32_t* lookback) {
+                                                                    uint32_t* ticket, uint32_t* lookback, int use_match) {
   constexpr int TILE_ITEMS = SORT_THREADS * ITEMS;
   constexpr int NW = SORT_THREADS / 32;
   __shared__ KeyT s_keys[TILE_ITEMS];
@@ -328,7 +330,9 @@ __global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? (ITEMS <= 
     for (int i = 0; i < CH; ++i) {
       if (c + i < ITEMS) {
         const uint32_t d = (uint32_t)(key[c + i] >> shift) & digit_mask;
-        peers[i] = warp_peers(d, nbits);
+        // most significant pass: a warp holds few distinct digits (depth keys share their top byte, the 32
+        // consecutive pairs of a warp come from a handful of Gaussians), where one MATCH.ANY beats nbits ballots
+        peers[i] = use_match ? __match_any_sync(0xffffffffu, d) : warp_peers(d, nbits);
       }
     }
 #pragma unroll
@@ -497,6 +501,7 @@ static cudaError_t sort_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint3
                              void* scratch, cudaStream_t s) {
   if (capacity <= 0 || npass <= 0) return cudaSuccess;
   if (npass > MAX_PASSES) return cudaErrorInvalidValue;
+  static const bool match_last = [] { const char* e = getenv("PDGS_SORT_MATCH"); return e ? atoi(e) != 0 : true; }();
   SortScratch sc = carve_sort_scratch(scratch, capacity, SORT_THREADS * ITEMS, npass);  // callers size for >= npass
   cudaError_t e = cudaMemsetAsync(scratch, 0, sc.zero_bytes, s);
   if (e != cudaSuccess) return e;
@@ -515,7 +520,8 @@ static cudaError_t sort_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint3
     const int nb = (end_bit - p * RADIX_BITS < RADIX_BITS) ? end_bit - p * RADIX_BITS : RADIX_BITS;
     sort_onesweep_kernel<KeyT, ITEMS><<<tiles, SORT_THREADS, 0, s>>>(
         kin, (p == 0 && iota_vals) ? nullptr : vin, kout, vout, n_dev, n_host, capacity, p * RADIX_BITS, (1u << nb) - 1u,
-        sc.hist + p * RADIX, sc.tickets + p, sc.lookback + (size_t)p * sc.ntiles * RADIX);
+        sc.hist + p * RADIX, sc.tickets + p, sc.lookback + (size_t)p * sc.ntiles * RADIX,
+        (match_last && npass >= 2 && p == npass - 1) ? 1 : 0);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     KeyT* tk = kin; kin = kout; kout = tk;
