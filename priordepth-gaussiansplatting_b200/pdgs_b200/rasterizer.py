@@ -181,7 +181,8 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
            grad_cov3Ds_precomp[P,6], grad_sh[P,M,3], grad_scales[P,3], grad_rotations[P,4]).
 
     accumulate_into (extension used by the view-parallel path): a dict of preallocated gradient
-    tensors keyed like PdgsGrads; the kernel adds into them instead of writing fresh tensors.
+    tensors keyed like PdgsGrads; the kernel adds into them instead of writing fresh tensors (or overwrites them when
+    the dict has "overwrite": True); "densify_grad_accum" / "densify_denom" / "max_radii2D" receive the statistics.
     dc / raw_params: as in rasterize_gaussians; with `dc` the tuple gains a ninth element grad_dc[P,1,3] and grad_sh is
     the gradient of features_rest; with raw_params the opacity / scale / rotation gradients are w.r.t. the raw tensors."""
     global LAUNCHES_BACKWARD
@@ -229,7 +230,9 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
             ddc = a.get("shs_dc")
             if dc is not None:
                 dsh = a.get("shs_rest")
-            g.accumulate = 1
+            # "overwrite": True -> the kernel writes every row of the given tensors (zeros for culled Gaussians) instead of
+            # adding to them; the densification statistics are still accumulated
+            g.accumulate = 0 if a.get("overwrite") else 1
         g.means3D, g.means2D = _ptr(dmeans3D), _ptr(dmeans2D)
         if dc is not None:
             g.shs_dc, g.shs_rest = _ptr(ddc), _ptr(dsh)

@@ -175,3 +175,39 @@ def test_batch_step_split_raw_equals_sum_of_single_view_autograd():
     for k, seg in names.items():
         e = helpers.rel_err(vp.buf.view(seg), sums[k].view_as(vp.buf.view(seg)))
         assert e < 1e-4, (k, e)
+
+
+def test_overwrite_mode_with_densification_statistics():
+    """accumulate_into={..., "overwrite": True}: every gradient row is written (garbage in the buffers does not matter,
+    culled rows become zero) while the densification statistics are still accumulated."""
+    from pdgs_b200 import rasterizer as rz
+    sc = scenes.camera_relative_scene("ow", 31, 4000, 128, 96, 3.0)
+    view = sc.views[0]
+    rs = helpers.cuda_settings(sc, view, DEV)
+    lv, color, radii, invd = helpers.run_cuda(sc, view, DEV)
+    gc, gd = cotangents(color, invd, 2)
+    fn = color.grad_fn
+    geom, binning, img = fn.saved_tensors[8], fn.saved_tensors[9], fn.saved_tensors[10]  # before backward frees them
+    num_rendered = fn.num_rendered
+    binning._pdgs_capacity = fn.binning_capacity
+    torch.autograd.backward([color, invd], [gc.to(DEV), gd.to(DEV)])
+    P = sc.P
+    f32 = dict(dtype=torch.float32, device=DEV)
+    acc = dict(means3D=torch.full((P, 3), 7.0, **f32), means2D=torch.full((P, 3), 7.0, **f32), shs=torch.full((P, 16, 3), 7.0, **f32),
+               opacities=torch.full((P, 1), 7.0, **f32), scales=torch.full((P, 3), 7.0, **f32), rotations=torch.full((P, 4), 7.0, **f32),
+               densify_grad_accum=torch.ones(P, **f32), densify_denom=torch.ones(P, **f32),
+               max_radii2D=torch.zeros(P, dtype=torch.int32, device=DEV), overwrite=True)
+    empty = torch.empty(0, device=DEV)
+    d = {k: v.detach() for k, v in lv.items() if v is not None}
+    rz.rasterize_gaussians_backward(rs.bg, d["means3D"], radii, empty, d["opacities"], d["scales"], d["rotations"], 1.0, empty,
+                                    rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, gc.to(DEV), gd.to(DEV), d["shs"],
+                                    rs.sh_degree, rs.campos, geom, num_rendered, binning, img, False, False, accumulate_into=acc)
+    for k in ("means3D", "shs", "opacities", "scales", "rotations"):
+        assert helpers.rel_err(acc[k], lv[k].grad.view_as(acc[k])) <= 1e-4, k
+    vis = radii > 0
+    assert float(acc["means3D"][~vis].abs().max()) == 0.0
+    expect = torch.ones(P, device=DEV)
+    expect[vis] += lv["means2D"].grad[vis, :2].norm(dim=-1)
+    assert helpers.rel_err(acc["densify_grad_accum"], expect) <= 1e-5
+    assert torch.equal(acc["densify_denom"], 1.0 + vis.float())
+    assert torch.equal(acc["max_radii2D"], radii * vis)

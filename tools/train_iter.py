@@ -80,7 +80,7 @@ f32 = dict(dtype=torch.float32, device=dev)
 grads = dict(means3D=torch.empty(P, 3, **f32), means2D=torch.empty(P, 3, **f32), shs_dc=torch.empty(P, 1, 3, **f32),
              shs_rest=torch.empty(P, 15, 3, **f32), opacities=torch.empty(P, 1, **f32), scales=torch.empty(P, 3, **f32),
              rotations=torch.empty(P, 4, **f32), densify_grad_accum=torch.zeros(P, **f32), densify_denom=torch.zeros(P, **f32),
-             max_radii2D=torch.zeros(P, dtype=torch.int32, device=dev))
+             max_radii2D=torch.zeros(P, dtype=torch.int32, device=dev), overwrite=True)  # K9 writes every gradient row
 loss_acc = torch.zeros(3, **f32)
 ssim_scratch = torch.empty(rz.ssim_scratch_bytes(W, H), dtype=torch.uint8, device=dev)
 empty = torch.empty(0, device=dev)
@@ -89,9 +89,6 @@ NAMES = dict(xyz="means3D", f_dc="shs_dc", f_rest="shs_rest", opacity="opacities
 
 def iter_fused():
     with torch.no_grad():
-        for k, g in NAMES.items():  # the accumulating backward adds into these rows (visible Gaussians only)
-            grads[g].zero_()
-        grads["means2D"].zero_()
         R, color, radii, geom, binning, img, invd = rz.rasterize_gaussians(
             rs.bg, pb["xyz"], empty, pb["opacity"], pb["scaling"], pb["rotation"], 1.0, empty, rs.viewmatrix, rs.projmatrix,
             rs.tanfovx, rs.tanfovy, H, W, pb["f_rest"], rs.sh_degree, rs.campos, False, False, False, dc=pb["f_dc"], raw_params=True)
