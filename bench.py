@@ -360,7 +360,6 @@ def main():
     # ---------------- end-to-end with host buffers (`e2e`) ----------------
     e2e = None
     if not args.no_e2e:
-        h2d = sum(v.numel() * 4 for v in host.values()) + sum(cam_host[i].numel() * 4 + tgt_host[i].numel() * 4 for i in my)
         d2h = 12  # the three loss sums
 
         staged = [None]
@@ -383,6 +382,7 @@ def main():
         for _ in range(max(1, min(args.warmup, 2))):
             e2e_step(prefetch_next=False)
         barrier()
+        h2d0 = vp.h2d_bytes
         t0 = time.perf_counter()
         e0.record()
         for k in range(args.steps):
@@ -391,6 +391,9 @@ def main():
         barrier()
         wall = (time.perf_counter() - t0) * 1e3
         t = torch.tensor([max(wall, e0.elapsed_time(e1))], dtype=torch.float64, device=dev)
+        # bytes actually copied host -> device per step by this rank: Gaussians (first step: the whole replica; later steps:
+        # this rank's 1/world share, the rest arrives by all-gather over NVLink), target images, camera blocks
+        h2d = (vp.h2d_bytes - h2d0) // args.steps + sum(cam_host[i].numel() * 4 for i in my)
         hb = torch.tensor([h2d, d2h], dtype=torch.int64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -398,8 +401,8 @@ def main():
         e2e = dict(value=n_views * args.steps / (float(t.item()) * 1e-3), unit=UNIT, h2d_bytes_per_step=int(hb[0].item()),
                    d2h_bytes_per_step=int(hb[1].item()), ms_per_step=float(t.item()) / args.steps,
                    api="pdgs_b200.viewparallel.ViewParallelRasterizer.step (C ABI: pdgs_forward / pdgs_image_loss / "
-                       "pdgs_backward) fed from pinned host tensors; step k+1's Gaussian upload overlaps step k (copy stream), "
-                       "target images are uploaded one view ahead",
+                       "pdgs_backward) fed from pinned host tensors; step k+1's Gaussians are uploaded during step k (each rank its "
+                       "1/world share over PCIe, replicas completed by an all-gather over NVLink), target images one view ahead",
                    loss_mean=float(last[0].item()) / n_views)
 
     if rank != 0:

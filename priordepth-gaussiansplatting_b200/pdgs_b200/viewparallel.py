@@ -16,6 +16,7 @@ CPU tensors with `gloo` by the tests, which inject their own per-view gradient f
 from __future__ import annotations
 
 import os
+import threading
 from typing import Callable, Dict, List, Optional, Sequence
 
 import torch
@@ -153,8 +154,9 @@ class ViewParallelRasterizer:
         self.lanes = max(1, int(lanes if lanes is not None else os.environ.get("PDGS_LANES", "3")))
         self._pool = None
         self._lane_streams = []
+        self.h2d_bytes = 0  # bytes this object copied host -> device (parameters and per-view images)
+        self._count_lock = threading.Lock()
         self._copy_stream = None
-        self._param_stream = None
         self._color_grads = None
 
     def _upload(self, i, targets, priors, masks):
@@ -164,48 +166,70 @@ class ViewParallelRasterizer:
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(self.device)
         with torch.cuda.stream(self._copy_stream):
+            with self._count_lock:
+                self.h2d_bytes += sum(t.numel() * t.element_size() for t in items if t is not None and t.device != self.device)
             items = [None if t is None else t.to(self.device, non_blocking=True) for t in items]
             ev = torch.cuda.Event()
             ev.record(self._copy_stream)
         return items, ev
 
     def stage_gaussians(self, host: Dict[str, torch.Tensor]):
-        """Start copying a dict of (pinned) host tensors -- the Gaussian parameters of an upcoming step -- to the device on
-        the copy stream and return a handle for step(gaussians=handle).  Called before the loss of the current step
-        is read back, it lets the next step's 236 B/Gaussian upload overlap this step's kernels."""
+        """Copy a dict of (pinned) host tensors -- the Gaussian parameters of an upcoming step -- to the device and return a
+        handle for step(gaussians=handle).  With several ranks each rank uploads its 1/world share and an all-gather over
+        NVLink completes the replicas (so every rank must call this together).  To overlap the upload with a running step
+        use step(prefetch_gaussians=...) instead, which slices the copy behind the per-view image uploads."""
         if self.device.type != "cuda":
             return dict(host), None
-        if self._param_stream is None:  # its own stream: the per-view image uploads must not queue behind it
-            self._param_stream = torch.cuda.Stream(self.device)
-        with torch.cuda.stream(self._param_stream):
-            g = {k: (v.to(self.device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in host.items()}
-            ev = torch.cuda.Event()
-            ev.record(self._param_stream)
-        return g, ev
+        plan = self._prefetch_begin(host)
+        self._prefetch_slice(plan, 0, 1)
+        return self._prefetch_end(plan)
 
     def _prefetch_begin(self, host: Dict[str, torch.Tensor]):
+        """Device buffers for the next step's Gaussians.  With several ranks every rank uploads only its 1/world share of
+        each tensor over PCIe; _prefetch_end completes the replicas with an all-gather over NVLink (the parameters are
+        identical on all ranks, so sending them world times through the host's memory system is the slow way)."""
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(self.device)
+        world, rank = self.world, self.rank
+        plan = {}
         with torch.cuda.stream(self._copy_stream):  # allocated on the stream that fills them
-            dev = {k: (torch.empty(v.shape, dtype=v.dtype, device=self.device) if torch.is_tensor(v) else v)
-                   for k, v in host.items()}
-        return host, dev
-
-    def _prefetch_slice(self, nxt, k: int, n: int) -> None:
-        host, dev = nxt
-        with torch.cuda.stream(self._copy_stream):
             for name, src in host.items():
                 if not torch.is_tensor(src):
+                    plan[name] = src
                     continue
-                s, d = src.reshape(-1), dev[name].view(-1)
-                a, b = s.numel() * k // n, s.numel() * (k + 1) // n
-                if b > a:
-                    d[a:b].copy_(s[a:b], non_blocking=True)
+                n = src.numel()
+                chunk = (n + world - 1) // world
+                flat = torch.empty(max(world * chunk, 1), dtype=src.dtype, device=self.device)
+                plan[name] = (flat, src.reshape(-1), n, chunk, min(rank * chunk, n), min((rank + 1) * chunk, n), tuple(src.shape))
+        return plan
 
-    def _prefetch_end(self, nxt):
-        ev = torch.cuda.Event()
-        ev.record(self._copy_stream)
-        return nxt[1], ev
+    def _prefetch_slice(self, plan, k: int, n_slices: int) -> None:
+        with torch.cuda.stream(self._copy_stream):
+            for name, p in plan.items():
+                if not isinstance(p, tuple):
+                    continue
+                flat, src, n, chunk, lo, hi = p[:6]
+                a, b = lo + (hi - lo) * k // n_slices, lo + (hi - lo) * (k + 1) // n_slices
+                if b > a:
+                    flat[a:b].copy_(src[a:b], non_blocking=True)
+                    with self._count_lock:
+                        self.h2d_bytes += (b - a) * src.element_size()
+
+    def _prefetch_end(self, plan):
+        world, rank = self.world, self.rank
+        dev = {}
+        with torch.cuda.stream(self._copy_stream):
+            for name, p in plan.items():
+                if not isinstance(p, tuple):
+                    dev[name] = p
+                    continue
+                flat, src, n, chunk, lo, hi, shape = p
+                if world > 1 and chunk > 0:  # in place: this rank's share already sits at its position in `flat`
+                    dist.all_gather_into_tensor(flat[:world * chunk], flat[rank * chunk:(rank + 1) * chunk], group=self.group)
+                dev[name] = flat[:n].view(shape)
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+        return dev, ev
 
     def _await(self, staged):
         items, ev = staged
@@ -239,7 +263,9 @@ class ViewParallelRasterizer:
         prefetch_gaussians: pinned HOST tensors of the NEXT step's Gaussians.  They are uploaded during this step, one
         slice per view, on the same copy stream and behind that view's image upload (host->device copies of different
         streams share one DMA queue, so a single 236 B/Gaussian copy issued up front would hold the images back and
-        stall the kernels); the handle comes back as out["prefetched"] and is passed as `gaussians` to the next step."""
+        stall the kernels); with several ranks each rank uploads 1/world of every tensor and an all-gather over NVLink
+        completes the replicas.  The handle comes back as out["prefetched"] and is passed as `gaussians` to the next
+        step.  Every rank must pass prefetch_gaussians in the same steps (it contains a collective)."""
         if isinstance(gaussians, tuple):  # handle from stage_gaussians(): wait for the upload on the compute stream
             gaussians, ev = gaussians
             if ev is not None:
