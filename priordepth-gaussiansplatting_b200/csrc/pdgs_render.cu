@@ -11,7 +11,11 @@
 //    (exact minimum of the quadratic over each 8x4 pixel box, with a conservative margin) and
 //    stores an 8-bit patch mask.  Each warp ballots its bit and visits only the survivors.  A
 //    culled Gaussian would have been rejected by every pixel of the patch, so images, n_contrib
-//    and gradients are unchanged; list positions stay those of the un-culled list.
+//    and gradients are unchanged; list positions stay those of the un-culled list.  The forward
+//    leaves each pair's mask in the binning buffer (pair_mask); the backward reads it back instead
+//    of recomputing it and skips the record gathers of pairs that reach no patch (35 % on C4).
+//    Computing the masks earlier, in duplicateWithKeys, was measured and is slower overall: here
+//    the arithmetic fills issue slots that the staging phase leaves idle.
 //  * Backward in two phases per warp.  Phase 1 (lane = pixel) walks the survivors back to front
 //    and, per (pixel, Gaussian), produces just two scalars: w = alpha*T and z = o*G*dL/dalpha.  The
 //    state carried between entries is T and one scalar (sum of w_j q_j of the entries behind), not

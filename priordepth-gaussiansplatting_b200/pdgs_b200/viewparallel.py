@@ -36,6 +36,13 @@ def shard_views(n_views: int, rank: int, world: int) -> range:
     return range(lo, lo + base + (1 if rank < rem else 0))
 
 
+def shard_span(numel: int, rank: int, world: int):
+    """(chunk, lo, hi): rank r uploads elements [lo, hi) of a flat parameter tensor; chunks are equal (all-gather needs
+    equal counts), so the padded buffer holds world * chunk >= numel elements and the last shares may be short or empty."""
+    chunk = (int(numel) + world - 1) // world
+    return chunk, min(rank * chunk, numel), min((rank + 1) * chunk, numel)
+
+
 class GradBuffer:
     """One flat fp32 buffer holding every per-Gaussian gradient plus the densification statistics
     (61 floats per Gaussian for SH degree 3), each segment starting on a 16-byte boundary so the kernels'
@@ -198,9 +205,9 @@ class ViewParallelRasterizer:
                     plan[name] = src
                     continue
                 n = src.numel()
-                chunk = (n + world - 1) // world
+                chunk, lo, hi = shard_span(n, rank, world)
                 flat = torch.empty(max(world * chunk, 1), dtype=src.dtype, device=self.device)
-                plan[name] = (flat, src.reshape(-1), n, chunk, min(rank * chunk, n), min((rank + 1) * chunk, n), tuple(src.shape))
+                plan[name] = (flat, src.reshape(-1), n, chunk, lo, hi, tuple(src.shape))
         return plan
 
     def _prefetch_slice(self, plan, k: int, n_slices: int) -> None:

@@ -90,3 +90,37 @@ def test_bias_corrected_matches_torch_adam_on_gpu():
     for k in P:
         d = float((a[k] - b[k]).abs().max())
         assert d <= 4e-6 * LRS[k] / 1e-4 + 4e-7 * float(b[k].abs().max()), (k, d)
+
+
+def test_edge_shapes_unaligned_and_generic_row_length():
+    """Row lengths without a compiled specialisation (M = 2, 7), tensors that start 4 bytes off a 16-byte boundary (scalar
+    path), N = 0, and more than 8 groups (chunked launches): still bit-exact."""
+    rng = np.random.default_rng(1)
+    N = 1237
+    vis = rng.random(N) < 0.5
+    mask = torch.from_numpy(vis).to(DEV)
+    groups, refs = [], []
+    for gi, M in enumerate([2, 7, 1, 3, 4, 45, 48, 5, 9, 16]):
+        p, g = rng.standard_normal((N, M)).astype(np.float32), rng.standard_normal((N, M)).astype(np.float32)
+        m, v = np.abs(rng.standard_normal((N, M))).astype(np.float32) * 1e-3, np.abs(rng.standard_normal((N, M))).astype(np.float32) * 1e-6
+        def dev(a, off):
+            buf = torch.empty(a.size + 4, dtype=torch.float32, device=DEV)
+            t = buf[off:off + a.size].view(a.shape)   # off = 1: 4 bytes past the 16-byte boundary
+            t.copy_(torch.from_numpy(a))
+            return t
+        off = gi % 2
+        tp, tg, tm, tv = dev(p, off), dev(g, off), dev(m, off), dev(v, off)
+        lr = 10.0 ** rng.uniform(-4, -2)
+        groups.append((tp, tg, tm, tv, lr))
+        sparse_adam_step(p, g, m, v, vis, lr, eps=1e-15)
+        refs.append((p, m, v))
+    sparse_adam_update(groups, mask, N, 0.9, 0.999, 1e-15, 0)
+    torch.cuda.synchronize()
+    for (tp, tg, tm, tv, lr), (p, m, v) in zip(groups, refs):
+        np.testing.assert_array_equal(tp.cpu().numpy().view(np.uint32), p.view(np.uint32))
+        np.testing.assert_array_equal(tm.cpu().numpy().view(np.uint32), m.view(np.uint32))
+        np.testing.assert_array_equal(tv.cpu().numpy().view(np.uint32), v.view(np.uint32))
+    with pytest.raises(Exception):
+        sparse_adam_update([(groups[0][0], groups[0][1], groups[0][2], groups[0][3], 1e-3)], mask.float(), N)  # bad mask dtype
+    with pytest.raises(Exception):
+        sparse_adam_update([(groups[0][0], groups[0][1], groups[0][2], groups[0][3], 1e-3)], mask[:-1], N)   # wrong length

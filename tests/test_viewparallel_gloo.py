@@ -23,6 +23,21 @@ def test_shard_views_partitions_contiguously():
             assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
 
 
+def test_parameter_upload_shares_cover_the_tensor():
+    from pdgs_b200.viewparallel import shard_span
+    for numel in (0, 1, 7, 48, 9_000_001):
+        for world in (1, 2, 3, 8):
+            spans = [shard_span(numel, r, world) for r in range(world)]
+            chunk = spans[0][0]
+            assert all(s[0] == chunk for s in spans) and world * chunk >= numel
+            covered = 0
+            for r, (_, lo, hi) in enumerate(spans):
+                assert lo == min(r * chunk, numel) and lo <= hi <= numel and hi - lo <= chunk
+                assert lo == covered or hi == lo  # contiguous, in rank order
+                covered = max(covered, hi)
+            assert covered == numel
+
+
 def test_grad_buffer_layout():
     for P in (0, 1, 5, 1001):
         b = GradBuffer(P, 16, "cpu")
