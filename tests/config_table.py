@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""Per-config timing through the reference-facing Python boundary (SURVEY.md 8(d) timing protocol).
+"""Per-config timing AND parity table through the reference-facing Python boundary (SURVEY.md 8(d) timing protocol).
+Lives under tests/ because it uses the oracle as a checker (only tests/, smoke() and bench.py's CPU legs may touch oracle/).
 
 For each BASELINE.json config (C1, C2, C3, C4 single view, C5 forward-only) this runs
 `diff_gaussian_rasterization.GaussianRasterizer.forward` + `.backward()` of an L1 image loss (C3 adds the masked
@@ -7,7 +8,7 @@ inverse-depth L1 of /root/reference/train.py:174), CUDA events around forward an
 W warm-up + K timed iterations, median / p10 / p90.  It also checks, at FULL size, radii and num_rendered against
 the fp32 bit-model (oracle/, checker only) and times the float64 CPU oracle on a tile window (bench.py's CPU arm).
 
-  python tools/config_table.py [--configs C1 C2 C3 C4 C5] [--iters 50] [--warmup 10] [--json out.json]
+  python tests/config_table.py [--configs C1 C2 C3 C4 C5] [--iters 50] [--warmup 10] [--json out.json]
 
 Prints one JSON object per config and a markdown table row for BASELINE.md section 4.
 """
