@@ -80,6 +80,47 @@ __device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, floa
   const float hA = 0.5f * A, hC = 0.5f * C;
   const float sx = -B * __fdividef(1.0f, A);  // argmin over dx on a row dy = const:  dx* = sx * dy
   const float sy = -B * __fdividef(1.0f, C);  // argmin over dy on a column dx = const
+#ifndef PDGS_MASK_FAST
+#define PDGS_MASK_FAST 1
+#endif
+#if PDGS_MASK_FAST
+  // Per column box k: nearest x to the centre cx, and the x-only parts of the form at that x; per row box m likewise.
+  // A box then costs two clamps and four FMAs.  The rounding margin is one absolute bound for the whole tile
+  // (1e-5 of the largest magnitude the three terms can reach on it) instead of a relative one per box.
+  float x0[2], cx[2], ak[2], bk[2], sk[2], y0[4], y1[4], cy[4], cm[4], dm[4], rm[4];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    x0[k] = (tx0 + 8.0f * k) - gx;  // pixel-centre box relative to the Gaussian
+    cx[k] = fminf(fmaxf(0.f, x0[k]), x0[k] + 7.0f);
+    bk[k] = B * cx[k];
+    ak[k] = hA * cx[k] * cx[k];
+    sk[k] = sy * cx[k];
+  }
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    y0[m] = (ty0 + 4.0f * m) - gy;
+    y1[m] = y0[m] + 3.0f;
+    cy[m] = fminf(fmaxf(0.f, y0[m]), y1[m]);
+    dm[m] = B * cy[m];
+    cm[m] = hC * cy[m] * cy[m];
+    rm[m] = sx * cy[m];
+  }
+  const float X = fmaxf(fabsf(x0[0]), fabsf(x0[1] + 7.0f)), Y = fmaxf(fabsf(y0[0]), fabsf(y1[3]));
+  const float taum = fmaf(1e-5f, fmaf(hA * X, X, fmaf(fabsf(B) * X, Y, hC * Y * Y)), tau);
+  uint32_t mask = 0;
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      // the box minimum of a convex quadratic centred outside the box lies on an edge facing the centre
+      const float dyv = fminf(fmaxf(sk[k], y0[m]), y1[m]);
+      const float q1 = fmaf(dyv, fmaf(hC, dyv, bk[k]), ak[k]);
+      const float dxv = fminf(fmaxf(rm[m], x0[k]), x0[k] + 7.0f);
+      const float q2 = fmaf(dxv, fmaf(hA, dxv, dm[m]), cm[m]);
+      if (!(fminf(q1, q2) > taum)) mask |= 1u << (m * 2 + k);
+    }
+  }
+#else
   float x0[2], cx[2], y0[4], cy[4];
 #pragma unroll
   for (int k = 0; k < 2; ++k) {
@@ -106,6 +147,7 @@ __device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, floa
       if (!(fminf(q1, q2) > tau)) mask |= 1u << (m * 2 + k);
     }
   }
+#endif
   return mask;
 }
 
