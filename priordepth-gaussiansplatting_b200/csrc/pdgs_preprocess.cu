@@ -194,6 +194,7 @@ __global__ void __launch_bounds__(PRE_THREADS, PDGS_PRE_CTAS) preprocess_kernel(
   g.tiles_touched[idx] = (uint32_t)((go.rx1 - go.rx0) * (go.ry1 - go.ry0));
 }
 
+// K8+K9 for scenes with precomputed colours (no SH): one thread per Gaussian, plain loads and stores.
 __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(DeviceArgs a, GeomView g,
                                                                         const int32_t* __restrict__ radii,
                                                                         const float* __restrict__ acc, GradPtrs gp) {
@@ -202,7 +203,6 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
   const int64_t idx = (int64_t)blockIdx.x * PRE_THREADS + threadIdx.x;
   if (idx >= a.P) return;
   const bool vis = radii[idx] > 0;
-  const int M = a.M;
   if (!vis) {
     if (!gp.accumulate) {  // dense zero rows for culled Gaussians
       if (gp.means3D) { gp.means3D[3 * idx] = 0.f; gp.means3D[3 * idx + 1] = 0.f; gp.means3D[3 * idx + 2] = 0.f; }
@@ -214,15 +214,6 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
       if (gp.cov3D_precomp) {
 #pragma unroll
         for (int k = 0; k < 6; ++k) gp.cov3D_precomp[6 * idx + k] = 0.f;
-      }
-      if (gp.shs) {
-        if (M == 16) {
-          float4* dst = reinterpret_cast<float4*>(gp.shs + (size_t)idx * 48);
-#pragma unroll
-          for (int k = 0; k < 12; ++k) dst[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        } else {
-          for (int k = 0; k < 3 * M; ++k) gp.shs[(size_t)idx * 3 * M + k] = 0.f;
-        }
       }
     }
     return;
@@ -261,61 +252,13 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
   geometry_backward(cam, mx, my, mz, cov, opacity, in, g_mean, g_op, g_cov);
   if (a.raw) g_op = raw_opacity_backward(opacity, g_op);
 
-  // colour
-  if (a.colors_precomp) {
-    if (gp.colors_precomp) {
-      if (gp.accumulate) {
-        red_add(gp.colors_precomp + 3 * idx, in.g_rgb[0]); red_add(gp.colors_precomp + 3 * idx + 1, in.g_rgb[1]);
-        red_add(gp.colors_precomp + 3 * idx + 2, in.g_rgb[2]);
-      } else {
-        gp.colors_precomp[3 * idx] = in.g_rgb[0]; gp.colors_precomp[3 * idx + 1] = in.g_rgb[1]; gp.colors_precomp[3 * idx + 2] = in.g_rgb[2];
-      }
-    }
-  } else {
-    float grgb[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) grgb[c] = ((in.clamped >> c) & 1u) ? 0.f : in.g_rgb[c];
-    const float dx = mx - cam.campos[0], dy = my - cam.campos[1], dz = mz - cam.campos[2];
-    float gdir[3], basis[16];
-    if (M == 16) {
-      ShRegs sh;
-      const float4* src = reinterpret_cast<const float4*>(a.shs + (size_t)idx * 48);
-#pragma unroll
-      for (int k = 0; k < 12; ++k) {
-        const float4 v = __ldg(src + k);
-        sh.v[4 * k] = v.x; sh.v[4 * k + 1] = v.y; sh.v[4 * k + 2] = v.z; sh.v[4 * k + 3] = v.w;
-      }
-      sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
+  // colour (this kernel only serves precomputed colours; SH scenes take preprocess_backward_sh_kernel)
+  if (gp.colors_precomp) {
+    if (gp.accumulate) {
+      red_add(gp.colors_precomp + 3 * idx, in.g_rgb[0]); red_add(gp.colors_precomp + 3 * idx + 1, in.g_rgb[1]);
+      red_add(gp.colors_precomp + 3 * idx + 2, in.g_rgb[2]);
     } else {
-      ShGlobal sh{a.shs + (size_t)idx * M * 3};
-      sh_backward_dir(cam.sh_degree, dx, dy, dz, sh, grgb, gdir, basis);
-    }
-    g_mean[0] += gdir[0]; g_mean[1] += gdir[1]; g_mean[2] += gdir[2];
-    if (gp.shs) {
-      const int n = sh_num_coeffs(cam.sh_degree);
-      if (M == 16) {
-        float out[48];
-#pragma unroll
-        for (int k = 0; k < 16; ++k) {
-          const float bk = (k < n) ? basis[k] : 0.f;
-          out[3 * k] = bk * grgb[0]; out[3 * k + 1] = bk * grgb[1]; out[3 * k + 2] = bk * grgb[2];
-        }
-        float4* dst = reinterpret_cast<float4*>(gp.shs + (size_t)idx * 48);
-#pragma unroll
-        for (int k = 0; k < 12; ++k) {
-          float4 v = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
-          if (gp.accumulate) red_add4(reinterpret_cast<float*>(dst + k), v.x, v.y, v.z, v.w); else dst[k] = v;
-        }
-      } else {
-        float* dst = gp.shs + (size_t)idx * 3 * M;
-        for (int k = 0; k < M; ++k) {
-          const float bk = (k < n) ? basis[k] : 0.f;
-          for (int c = 0; c < 3; ++c) {
-            const float v = bk * grgb[c];
-            if (gp.accumulate) red_add(dst + 3 * k + c, v); else dst[3 * k + c] = v;
-          }
-        }
-      }
+      gp.colors_precomp[3 * idx] = in.g_rgb[0]; gp.colors_precomp[3 * idx + 1] = in.g_rgb[1]; gp.colors_precomp[3 * idx + 2] = in.g_rgb[2];
     }
   }
   // covariance
