@@ -91,7 +91,10 @@ constexpr int PRE_SPLIT_SMEM = (PRE_THREADS / 32) * SPLIT_WARP_FLOATS * (int)siz
 // its shared-memory slice with coalesced 16-byte loads; each lane then reads its own 45-float row with stride 45
 // (odd, so conflict-free).  The 180-byte rows themselves are only 4-byte aligned, so per-thread vector loads are
 // not possible on this layout.
-__device__ __forceinline__ void warp_stage_rest(const float* __restrict__ rest, int64_t warp_row0, int64_t P, float* slice) {
+// vmask: lanes (rows) whose Gaussian is visible; a 16-byte piece is fetched only if one of the (at most two) rows it
+// overlaps is visible, so rows of culled Gaussians cost no DRAM traffic beyond the sectors they share with neighbours.
+__device__ __forceinline__ void warp_stage_rest(const float* __restrict__ rest, int64_t warp_row0, int64_t P, float* slice,
+                                                unsigned vmask) {
   const int lane = threadIdx.x & 31;
   const int64_t left = P - warp_row0;
   const float* src = rest + warp_row0 * SPLIT_REST;
@@ -101,7 +104,10 @@ __device__ __forceinline__ void warp_stage_rest(const float* __restrict__ rest, 
 #pragma unroll
     for (int i = 0; i < 12; ++i) {
       const int j = lane + 32 * i;
-      if (j < SPLIT_WARP_FLOATS / 4) d4[j] = __ldg(s4 + j);
+      if (j < SPLIT_WARP_FLOATS / 4) {
+        const int r0 = (4 * j) / SPLIT_REST, r1 = (4 * j + 3) / SPLIT_REST;
+        if (((vmask >> r0) | (vmask >> r1)) & 1u) d4[j] = __ldg(s4 + j);
+      }
     }
   } else {
     const int n = (int)(left > 0 ? left : 0) * SPLIT_REST;
@@ -140,7 +146,8 @@ __global__ void __launch_bounds__(PRE_THREADS, PDGS_PRE_CTAS) preprocess_kernel(
   float* slice = nullptr;
   if (SPLIT && a.M == 16) {
     slice = pre_stage + (threadIdx.x >> 5) * SPLIT_WARP_FLOATS;
-    if (__any_sync(0xffffffffu, vis)) warp_stage_rest(a.shs_rest, idx - (threadIdx.x & 31), a.P, slice);
+    const unsigned vmask = __ballot_sync(0xffffffffu, vis);
+    if (vmask) warp_stage_rest(a.shs_rest, idx - (threadIdx.x & 31), a.P, slice, vmask);
   }
   if (!in_range) return;
   if (!vis) {
