@@ -185,6 +185,26 @@ __device__ __forceinline__ void stage_entry(Stage& st, bool valid, uint32_t src,
   st.mask[threadIdx.x] = (uint8_t)m;
 }
 
+// Survivor loop indexing.  The survivor mask of 32 staged entries is bit-reversed, so its highest set bit `hb` is the
+// first remaining list entry j = 31 - hb of the block.  Written as PTX so that the address of that entry's record is
+// ONE multiply-add from the address of the block's last record (last - 16*hb) instead of the three integer
+// instructions the compiler derives from j (it canonicalises every C++ spelling back to 31 - hb, + block base, * 16).
+__device__ __forceinline__ uint32_t highest_bit(uint32_t m) {
+  uint32_t r;
+  asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(m));
+  return r;
+}
+__device__ __forceinline__ uint32_t record_addr(uint32_t last_addr, uint32_t hb) {
+  uint32_t r;
+  asm("mad.lo.u32 %0, %1, 0xfffffff0, %2;" : "=r"(r) : "r"(hb), "r"(last_addr));
+  return r;
+}
+__device__ __forceinline__ float4 lds128_nv(uint32_t a) {  // not volatile: the forward loop has no shared-memory stores
+  float4 v;
+  asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+
 #ifndef PDGS_FWD_CTAS
 #define PDGS_FWD_CTAS 5
 #endif
@@ -207,6 +227,8 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
   const float tx0 = (float)(blockIdx.x * TILE), ty0 = (float)(blockIdx.y * TILE);
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   const uint32_t wbit = 1u << warp;
+  const uint32_t st_addr = (uint32_t)__cvta_generic_to_shared(&st.a[0]);
+  constexpr uint32_t FWD_ST_B = (uint32_t)offsetof(Stage, b), FWD_ST_C = (uint32_t)offsetof(Stage, c);
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
   uint32_t last = 0, accepted = 0, tested = range.y - range.x;
   bool done = !inside;
@@ -220,12 +242,14 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
     for (int k = 0; k * 32 < cnt; ++k) {
       // survivors of this warp's patch, bit-reversed so that the leading one is the first list entry
       uint32_t rm = __brev(__ballot_sync(FULL, (st.mask[k * 32 + lane] & wbit) != 0));
+      const uint32_t last_rec = st_addr + 16u * (uint32_t)(k * 32 + 31);
       while (rm) {
-        const int lz = __clz(rm);
-        const int j = k * 32 + lz;
-        rm &= ~(0x80000000u >> lz);
-        const float4 a = st.a[j];
-        const float4 b = st.b[j];
+        const uint32_t hb = highest_bit(rm);
+        rm ^= 1u << hb;
+        const uint32_t rec = record_addr(last_rec, hb);
+        const int j = k * 32 + 31 - (int)hb;
+        const float4 a = lds128_nv(rec);
+        const float4 b = lds128_nv(rec + FWD_ST_B);
         const float dx = a.x - pxf, dy = a.y - pyf;
         const float t = gauss_exponent(dx, dy, a.z, a.w, b.x, b.y);
         const float alpha = fminf(ALPHA_MAX, ex2_approx(t));
@@ -236,7 +260,8 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
           tested = pos0 + j + 1;
           continue;
         }
-        const float2 c = make_float2(st.c[j].x, st.c[j].y);
+        float2 c;
+        asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(c.x), "=f"(c.y) : "r"(rec + FWD_ST_C));
         const float w = alpha * T;
         C0 = fmaf(b.w, w, C0);
         C1 = fmaf(c.x, w, C1);
@@ -455,20 +480,22 @@ __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(cons
       if (lo >= 32) continue;
       if (lo > 0) mw &= 0xffffffffu << lo;
       uint32_t rm = __brev(mw);  // leading one = first entry to visit
+      const uint32_t last_rec = sst + 16u * (uint32_t)(k * 32 + 31);
+      const uint32_t pos_last = top - (uint32_t)(k * 32 + 31);  // list position of the block's last entry (may wrap: only used + hb)
       while (rm) {
-        const int lz = __clz(rm);
-        const int j = k * 32 + lz;
-        rm &= ~(0x80000000u >> lz);
-        const float4 a = lds128(sst + 16 * j), b = lds128(sst + ST_B + 16 * j);
+        const uint32_t hb = highest_bit(rm);  // entry j = k*32 + 31 - hb
+        rm ^= 1u << hb;
+        const uint32_t rec = record_addr(last_rec, hb);
+        const float4 a = lds128(rec), b = lds128(rec + ST_B);
         const float dx = a.x - pxf, dy = a.y - pyf;
         const float t = gauss_exponent(dx, dy, a.z, a.w, b.x, b.y);
         const float araw = ex2_approx(t);  // o * G
         const float alpha = fminf(ALPHA_MAX, araw);
-        const uint32_t pos = top - (uint32_t)j;
+        const uint32_t pos = pos_last + hb;  // = top - j
         const bool active = (pos < last_contributor) && !(t > b.y) && !(alpha < ALPHA_MIN);
         if (__any_sync(FULL, active)) {
           float z = 0.f, w = 0.f;
-          const float4 c = lds128(sst + ST_C + 16 * j);  // uniform address: one broadcast wavefront
+          const float4 c = lds128(rec + ST_C);  // uniform address: one broadcast wavefront
           const uint32_t row_id = __float_as_uint(c.z);
           if (active) {
             const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
