@@ -425,7 +425,8 @@ def main():
         "preprocess": ("hbm", 12 * Pn + 224 * V + 12 * Pn + 40 * V),
         "depth_sort": ("hbm", 4 * Pn + 12 * Pn + 3 * 16 * Pn),
         "scan": ("hbm", 12 * Pn),
-        "duplicate": ("hbm", 8 * Pn + 20 * V + 8 * R),
+        # fused scan + duplicate: sorted order 4P, tile rects 8P gathered, point_offsets 4P written, 8-byte pairs written
+        "duplicate": ("hbm", 16 * Pn + 8 * R),
         "sort": ("hbm", 4 * R + npass * 16 * R),
         "ranges": ("hbm", 4 * R + 8 * T),
         "blend_fwd": ("fp32_simt", 15 * work["n_test"] / nv + 11 * work["n_acc"] / nv),

@@ -196,6 +196,125 @@ __global__ void __launch_bounds__(DUP_WARPS * 32) duplicate_kernel(GeomView g, i
   }
 }
 
+// K2 + K3 in one kernel (the steady-state path: a binning buffer is at hand).  A CTA takes DUP_TILE consecutive sorted
+// Gaussians, eight warps of DUP_SEG each.  The pair count of a Gaussian is the area of its tile rect (culled
+// Gaussians carry an empty rect), which the emit phase needs anyway, so tiles_touched is not gathered at all and the
+// offsets never travel through HBM between two kernels: warp scan -> CTA scan -> decoupled look-back over the CTAs
+// (tickets give the order, as in scan_kernel) -> emit.  point_offsets are still written (state view, resume path).
+// Pairs that would land at or beyond `capacity` are not written; the host sees R > capacity and re-runs with a larger
+// buffer through the resume path (duplicate_kernel above).
+static_assert(DUP_TILE == DUP_WARPS * DUP_SEG, "fused scan + duplicate tile");
+
+__global__ void __launch_bounds__(DUP_WARPS * 32) scan_duplicate_kernel(GeomView g, int64_t P, int grid_x,
+                                                                        uint32_t* __restrict__ tkeys,
+                                                                        uint32_t* __restrict__ vals, int64_t capacity) {
+  __shared__ uint32_t s_off[DUP_WARPS][DUP_SEG + 1];
+  __shared__ uint2 s_rect[DUP_WARPS][DUP_SEG];
+  __shared__ uint32_t s_idx[DUP_WARPS][DUP_SEG];
+  __shared__ uint32_t s_wsum[DUP_WARPS];
+  __shared__ uint32_t s_tile;
+  __shared__ unsigned long long s_excl;
+  if (threadIdx.x == 0) s_tile = atomicAdd(&g.ctrl->scan_ticket, 1u);
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t seg0 = ((int64_t)tile * DUP_WARPS + warp) * DUP_SEG;
+  const int n = (seg0 >= P) ? 0 : (int)((P - seg0 < DUP_SEG) ? (P - seg0) : DUP_SEG);
+  uint32_t* off = s_off[warp];
+  constexpr int K = DUP_SEG / 32;
+  uint32_t idx[K];
+  uint2 rc[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) idx[k] = (k * 32 + lane < n) ? g.order[seg0 + k * 32 + lane] : 0u;
+#pragma unroll
+  for (int k = 0; k < K; ++k) rc[k] = (k * 32 + lane < n) ? __ldg(g.rect + idx[k]) : make_uint2(0u, 0u);
+  uint32_t run = 0;  // pairs of the warp's Gaussians before block k
+  if (lane == 0) off[0] = 0u;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int j = k * 32 + lane;
+    uint32_t inc = ((rc[k].y & 0xffffu) - (rc[k].x & 0xffffu)) * ((rc[k].y >> 16) - (rc[k].x >> 16));
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += up;
+    }
+    off[j + 1] = run + inc;  // inclusive, relative to the warp's first pair
+    s_idx[warp][j] = idx[k];
+    s_rect[warp][j] = rc[k];
+    run += __shfl_sync(0xffffffffu, inc, 31);
+  }
+  if (lane == 0) s_wsum[warp] = run;
+  __syncthreads();
+  unsigned long long woff = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < DUP_WARPS; ++w) {
+    const unsigned long long c = s_wsum[w];
+    if (w < warp) woff += c;
+    total += c;
+  }
+  if (warp == 0) {
+    // warp-parallel decoupled look-back, as in scan_kernel
+    unsigned long long excl = 0;
+    if (lane == 0) st_relaxed_u64(&g.scan_state[tile], (tile == 0 ? FLAG_INC : FLAG_AGG) | total);
+    int64_t t = (int64_t)tile - 1;
+    while (t >= 0) {
+      const int64_t ti = t - lane;
+      unsigned long long sv = FLAG_INC;
+      if (ti >= 0) {
+        do { sv = ld_relaxed_u64(&g.scan_state[ti]); } while ((sv >> 62) == 0ull);
+      }
+      const unsigned incmask = __ballot_sync(0xffffffffu, (sv >> 62) == 2ull);
+      const int first = incmask ? (__ffs(incmask) - 1) : 31;
+      unsigned long long val = (lane <= first) ? (sv & VAL_MASK) : 0ull;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+      excl += val;
+      if (incmask) break;
+      t -= 32;
+    }
+    if (lane == 0) {
+      if (tile != 0) st_relaxed_u64(&g.scan_state[tile], FLAG_INC | (excl + total));
+      s_excl = excl;
+      const int64_t ntiles = (P + DUP_TILE - 1) / DUP_TILE;
+      if ((int64_t)tile == ntiles - 1) {
+        const unsigned long long R = excl + total;
+        g.ctrl->num_rendered = (uint32_t)(R > 0xffffffffull ? 0xffffffffull : R);
+        g.ctrl->overflow = (R >= (unsigned long long)MAX_PAIRS) ? 1u : 0u;
+      }
+    }
+  }
+  __syncthreads();
+  if (n == 0) return;
+  const unsigned long long base = s_excl + woff;  // pairs before this warp's first
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int j = k * 32 + lane;
+    if (j < n) g.point_offsets[seg0 + j] = (uint32_t)(base + off[j + 1]);
+  }
+  if (base >= (unsigned long long)capacity) return;
+  uint32_t total_w = off[n];
+  if (base + total_w > (unsigned long long)capacity) total_w = (uint32_t)((unsigned long long)capacity - base);
+  const uint32_t first = (uint32_t)base;  // < capacity <= 2^30
+  for (uint32_t e = lane; e < total_w; e += 32) {
+    // largest j in [0, n) with off[j] <= e  (off is non-decreasing; empty Gaussians have off[j] == off[j+1])
+    int lo = 0, hi = n;  // invariant: off[lo] <= e < off[hi]
+#pragma unroll
+    for (int it = 0; it < 7; ++it) {
+      const int mid = (lo + hi) >> 1;
+      if (hi - lo > 1) {
+        if (off[mid] <= e) lo = mid; else hi = mid;
+      }
+    }
+    const uint2 r = s_rect[warp][lo];
+    const uint32_t rx0 = r.x & 0xffffu, ry0 = r.x >> 16, w = (r.y & 0xffffu) - rx0;
+    const uint32_t local = e - off[lo];
+    const uint32_t dy = local / w, dx = local - dy * w;
+    tkeys[first + e] = (ry0 + dy) * (uint32_t)grid_x + rx0 + dx;
+    vals[first + e] = s_idx[warp][lo];
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // K4: onesweep LSD radix sort, 8-bit digits.  One histogram kernel for all passes, then one
 // chained-scan (decoupled look-back) kernel per pass.  look-back word: [31:30] flag, [29:0] count.
@@ -492,6 +611,14 @@ cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, uint32_t* tkeys, u
   const int64_t per_block = DUP_WARPS * DUP_SEG;
   const unsigned blocks = (unsigned)((a.P + per_block - 1) / per_block);
   duplicate_kernel<<<blocks, DUP_WARPS * 32, 0, s>>>(g, a.P, a.grid_x, tkeys, vals, capacity);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_scan_duplicate(const DeviceArgs& a, GeomView g, uint32_t* tkeys, uint32_t* vals, int64_t capacity,
+                                  cudaStream_t s) {
+  if (a.P <= 0) return cudaSuccess;
+  const unsigned blocks = (unsigned)((a.P + DUP_TILE - 1) / DUP_TILE);
+  scan_duplicate_kernel<<<blocks, DUP_WARPS * 32, 0, s>>>(g, a.P, a.grid_x, tkeys, vals, capacity);
   return cudaGetLastError();
 }
 

@@ -190,8 +190,10 @@ static int make_args(const PdgsScene* sc, const PdgsCamera* cam, DeviceArgs& a) 
     }                                                                                                 \
   } while (0)
 
+// fused_scan: the scan of tiles_touched has not run yet; one kernel scans and emits the pairs, and the pair count is
+// copied to the host behind it.  Otherwise (resume) point_offsets are valid and only the pairs are emitted.
 static int run_binning_and_blend(PdgsHandle* h, const DeviceArgs& a, GeomView g, ImageView im, PdgsState* st,
-                                 const int32_t* radii, const PdgsForwardOut* out, int debug, cudaStream_t s) {
+                                 const int32_t* radii, const PdgsForwardOut* out, int debug, bool fused_scan, cudaStream_t s) {
   BinningView b = carve_binning(st->binning, st->capacity_pairs);
   if (b.bytes > st->binning_bytes) return fail(PDGS_E_INVALID, "binning buffer smaller than pdgs_binning_bytes(capacity)");
   const int tiles = a.grid_x * a.grid_y;
@@ -200,7 +202,12 @@ static int run_binning_and_blend(PdgsHandle* h, const DeviceArgs& a, GeomView g,
   uint32_t* vin = (npass % 2 == 0) ? b.point_list : b.vals_b;
   {
     StageTimer t(h, PDGS_STAGE_DUPLICATE, s);
-    PD_STEP(debug, s, launch_duplicate(a, g, kin, vin, st->capacity_pairs, s));
+    if (fused_scan) PD_STEP(debug, s, launch_scan_duplicate(a, g, kin, vin, st->capacity_pairs, s));
+    else PD_STEP(debug, s, launch_duplicate(a, g, kin, vin, st->capacity_pairs, s));
+  }
+  if (fused_scan) {
+    PD_CUDA(cudaMemcpyAsync(h->host_slot, g.ctrl, 8, cudaMemcpyDeviceToHost, s));
+    PD_CUDA(cudaEventRecord(h->ev, s));
   }
   {
     StageTimer t(h, PDGS_STAGE_SORT, s);
@@ -235,7 +242,7 @@ int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, P
 
   if (!resume) {
     PD_CUDA(cudaMemsetAsync(g.ctrl, 0, sizeof(Ctrl), s));
-    PD_CUDA(cudaMemsetAsync(g.scan_state, 0, ((size_t)(a.P > 0 ? a.P : 1) + SCAN_TILE - 1) / SCAN_TILE * 8, s));
+    PD_CUDA(cudaMemsetAsync(g.scan_state, 0, ((size_t)(a.P > 0 ? a.P : 1) + DUP_TILE - 1) / DUP_TILE * 8, s));
     {
       StageTimer t(h, PDGS_STAGE_PREPROCESS, s);
       PD_STEP(debug, s, launch_preprocess(a, g, out->radii, s));
@@ -245,15 +252,16 @@ int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, P
       PD_STEP(debug, s, launch_sort_u32(g.depth_keys, g.order, g.depth_keys_b, g.order_b, true, nullptr, a.P, a.P,
                                         DEPTH_SORT_PASSES, 32, g.sort_scratch, s));
     }
-    {
-      StageTimer t(h, PDGS_STAGE_SCAN, s);
-      PD_STEP(debug, s, launch_scan(g, a.P, s));
-    }
-    PD_CUDA(cudaMemcpyAsync(h->host_slot, g.ctrl, 8, cudaMemcpyDeviceToHost, s));
-    PD_CUDA(cudaEventRecord(h->ev, s));
     if (have_binning) {
-      rc = run_binning_and_blend(h, a, g, im, state, out->radii, out, debug, s);
+      rc = run_binning_and_blend(h, a, g, im, state, out->radii, out, debug, true, s);
       if (rc != PDGS_OK) return rc;
+    } else {  // sizing call: only the pair count is wanted
+      {
+        StageTimer t(h, PDGS_STAGE_SCAN, s);
+        PD_STEP(debug, s, launch_scan(g, a.P, s));
+      }
+      PD_CUDA(cudaMemcpyAsync(h->host_slot, g.ctrl, 8, cudaMemcpyDeviceToHost, s));
+      PD_CUDA(cudaEventRecord(h->ev, s));
     }
     PD_CUDA(cudaEventSynchronize(h->ev));
     const unsigned long long slot = h->host_slot[0];
@@ -267,7 +275,7 @@ int pdgs_forward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, P
   // resume: geometry state is valid, R known; (re)run binning + blend with a big-enough buffer
   if (!have_binning) return fail(PDGS_E_INVALID, "resume without a binning buffer");
   if (*num_rendered > state->capacity_pairs) return fail(PDGS_E_INVALID, "resume: capacity < num_rendered");
-  return run_binning_and_blend(h, a, g, im, state, out->radii, out, debug, s);
+  return run_binning_and_blend(h, a, g, im, state, out->radii, out, debug, false, s);
 }
 
 int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, const PdgsState* state,

@@ -24,6 +24,7 @@ constexpr int DEPTH_SORT_PASSES = 4;
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;  // 4096 counts per CTA
+constexpr int DUP_TILE = 1024;  // sorted Gaussians per CTA of the fused scan + duplicate kernel (8 warps x 128)
 constexpr uint32_t MAX_PAIRS = 1u << 30;               // look-back words carry 30-bit counts
 
 // Control block at the start of the geometry blob (device memory, 256 B).
@@ -51,7 +52,7 @@ struct GeomView {
   uint32_t* depth_keys_b;   // [P] ping-pong buffers of the depth sort
   uint32_t* order_b;        // [P]
   uint32_t* point_offsets;  // [P] inclusive scan of tiles_touched taken in depth order
-  unsigned long long* scan_state;  // [ceil(P/SCAN_TILE)]
+  unsigned long long* scan_state;  // [ceil(P/DUP_TILE)] (the stand-alone scan uses the first ceil(P/SCAN_TILE) words)
   void* sort_scratch;       // depth-sort histograms / tickets / look-back words
   size_t sort_scratch_bytes;
   size_t bytes;
@@ -96,7 +97,7 @@ inline __host__ GeomView carve_geom(void* base, int64_t P) {
   v.depth_keys_b = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
   v.order_b = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
   v.point_offsets = (uint32_t*)(p + off); off += align_up(Pn * sizeof(uint32_t));
-  const size_t nscan = (Pn + SCAN_TILE - 1) / SCAN_TILE;
+  const size_t nscan = (Pn + DUP_TILE - 1) / DUP_TILE;
   v.scan_state = (unsigned long long*)(p + off); off += align_up(nscan * sizeof(unsigned long long));
   v.sort_scratch = (void*)(p + off);
   v.sort_scratch_bytes = carve_sort_scratch(nullptr, P, SORT_THREADS * SORT_ITEMS_U32, DEPTH_SORT_PASSES).bytes;
@@ -185,6 +186,8 @@ struct DeviceArgs {
 
 cudaError_t launch_preprocess(const DeviceArgs& a, GeomView g, int32_t* radii, cudaStream_t s);
 cudaError_t launch_scan(GeomView g, int64_t P, cudaStream_t s);
+cudaError_t launch_scan_duplicate(const DeviceArgs& a, GeomView g, uint32_t* tkeys, uint32_t* vals, int64_t capacity,
+                                  cudaStream_t s);
 cudaError_t launch_duplicate(const DeviceArgs& a, GeomView g, uint32_t* tkeys, uint32_t* vals, int64_t capacity,
                              cudaStream_t s);
 // Stable LSD radix sorts of (key, u32 value) pairs between buffers A and B.  The input must sit in A if npass is

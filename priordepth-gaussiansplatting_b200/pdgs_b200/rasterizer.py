@@ -152,8 +152,10 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
         rc = L.check(lib.pdgs_forward(h, C.byref(sc), C.byref(cam), C.byref(st), C.byref(out), 0, C.byref(R), stream),
                      "pdgs_forward")
         tiles = ((W + 15) // 16) * ((H + 15) // 16)
-        launches = 2 if P > 0 else 0                       # preprocess, scan
-        per_bin = 1 + 1 + _passes(tiles) + 1 + 1           # duplicate, histogram, passes, ranges, blend
+        launches = 1 if P > 0 else 0                       # preprocess
+        if P > 0 and cap == 0:
+            launches += 1                                  # stand-alone scan of the sizing call
+        per_bin = 1 + 2 + _passes(tiles) + 1 + 1           # scan + duplicate, 2 histograms, radix passes (4 depth + tile id), ranges, blend
         if cap > 0:
             launches += per_bin
         if rc == L.PDGS_NEED_BINNING:

@@ -184,3 +184,21 @@ def test_batch_step_guarded(guarded, monkeypatch, split_raw):
         vp.step(g, views, targets, priors, None, 0.5, lambda_dssim=lam)
     guarded.check()
     assert torch.isfinite(vp.buf.flat).all()
+
+
+def test_capacity_overflow_resume_guarded(guarded):
+    """A binning buffer sized from an earlier, smaller view: the fused scan + duplicate kernel must stop at the capacity,
+    report the true pair count, and the resumed call (stand-alone duplicate over the stored offsets) must give the same result."""
+    sc = ragged_scene(5003, 641, 359)
+    view = sc.views[0]
+    ref = fwd_bwd(sc, view)
+    dev = torch.device(DEV)
+    hint = rz._capacity_hint[dev]
+    assert hint > 6000
+    rz._capacity_hint[dev] = 1500
+    out = fwd_bwd(sc, view)
+    guarded.check()
+    assert rz._capacity_hint[dev] == hint
+    assert torch.equal(out[1], ref[1]) and torch.equal(out[0], ref[0]) and torch.equal(out[2], ref[2])
+    for k in ref[3]:
+        assert helpers.rel_err(out[3][k], ref[3][k]) < 1e-4, k
