@@ -150,9 +150,11 @@ size_t pdgs_image_bytes(int32_t width, int32_t height);
 size_t pdgs_binning_bytes(int64_t capacity_pairs, int64_t P);
 size_t pdgs_backward_scratch_bytes(int64_t P);
 
-/* Forward.  resume=0: preprocess + scan, then (if state->capacity_pairs > 0) the binning,
- * sort and blend are launched speculatively behind a device-side guard; the host waits only
- * for the pair count.  Returns PDGS_OK when the image is complete (enqueued), or
+/* Forward.  resume=0: preprocess + depth sort, then (if state->capacity_pairs > 0) scan +
+ * duplicateWithKeys (one kernel, timed as PDGS_STAGE_DUPLICATE), sort and blend are launched
+ * speculatively behind a device-side guard -- no pair is written at or beyond the capacity --
+ * and the host waits only for the pair count; without a binning buffer only the scan runs
+ * (PDGS_STAGE_SCAN).  Returns PDGS_OK when the image is complete (enqueued), or
  * PDGS_NEED_BINNING with *num_rendered set when the binning buffer is absent/too small:
  * allocate pdgs_binning_bytes(>= *num_rendered, P) and call again with resume=1, which runs
  * only duplicateWithKeys -> sort -> ranges -> blend on the state already in `geom`. */
