@@ -52,7 +52,8 @@ typedef struct PdgsCamera {
   const float* projmatrix;  /* [16] device */
   int32_t sh_degree;        /* active degree 0..3 */
   const float* campos;      /* [3]  device */
-  int32_t prefiltered;      /* accepted, ignored (culled points are simply skipped) */
+  int32_t prefiltered;      /* must be 0: the reference traps on a culled point when set and always passes False
+                             * (gaussian_renderer/__init__.py:47); pdgs_forward returns PDGS_E_INVALID for 1 */
   int32_t debug;            /* 1: synchronise + check after every kernel */
   int32_t antialiasing;
 } PdgsCamera;
@@ -185,10 +186,16 @@ int pdgs_sh_backward_views_split(PdgsHandle* h, const PdgsScene* scene, int32_t 
  *   loss[1] += mean |(invdepth - prior) * mask|          over H*W      (skipped when prior is NULL)
  *   dL_dcolor    = w_color * sign(color - target) / (3*H*W)
  *   dL_dinvdepth = w_depth * sign((invdepth - prior) * mask) * mask / (H*W)
- * mask may be NULL (= ones).  loss is a 2-float DEVICE accumulator the caller zeroes. */
+ * mask may be NULL (= ones).  loss is a 2-float DEVICE accumulator the caller zeroes.
+ * clamp01 / alpha_mask restate what the reference's caller does to the rendered image BEFORE the losses
+ * (/root/reference/gaussian_renderer/__init__.py:121 `rendered_image.clamp(0, 1)`; train.py:148-150
+ * `image *= alpha_mask`): the loss is taken on a = clamp(color, 0, 1) * alpha_mask (alpha_mask: one [H*W] plane
+ * shared by the three colour planes, NULL = ones) and dL_dcolor is the cotangent w.r.t. the RAW rasterizer output:
+ * dL/da * alpha_mask where 0 <= color <= 1, zero elsewhere (torch.clamp's backward). */
 int pdgs_image_loss(PdgsHandle* h, const float* color, const float* target, const float* invdepth,
-                    const float* prior, const float* mask, int32_t width, int32_t height, float w_color,
-                    float w_depth, float* dL_dcolor, float* dL_dinvdepth, float* loss, void* stream);
+                    const float* prior, const float* mask, const float* alpha_mask, int32_t clamp01, int32_t width,
+                    int32_t height, float w_color, float w_depth, float* dL_dcolor, float* dL_dinvdepth, float* loss,
+                    void* stream);
 
 /* SSIM with the 11x11 Gaussian window (sigma 1.5, zero "same" padding) on planar fp32 images [planes][H][W]; the
  * map-level interface of the reference's fused-ssim module:
@@ -210,11 +217,13 @@ size_t pdgs_ssim_scratch_bytes(int32_t width, int32_t height, int32_t planes);
  *   L = (1 - lambda_dssim) * mean|color - target| + lambda_dssim * (1 - mean ssim(color, target))
  *       + w_depth * mean|(invdepth - prior) * mask|
  *   loss[0] += mean L1, loss[1] += mean masked depth L1 (prior != NULL), loss[2] += mean SSIM   (DEVICE float[3])
- *   dL_dcolor = dL/dcolor, dL_dinvdepth = dL/dinvdepth.  scratch: pdgs_ssim_scratch_bytes(width, height, 3) bytes. */
+ *   dL_dcolor = dL/dcolor, dL_dinvdepth = dL/dinvdepth.  scratch: pdgs_ssim_scratch_bytes(width, height, 3) bytes.
+ * clamp01 / alpha_mask: as in pdgs_image_loss -- with clamp01 = 1 this is the reference's training loss on the raw
+ * rasterizer output (render() clamps, train.py masks, then l1_loss and fused_ssim see that image). */
 int pdgs_image_loss_ssim(PdgsHandle* h, const float* color, const float* target, const float* invdepth,
-                         const float* prior, const float* mask, int32_t width, int32_t height, float lambda_dssim,
-                         float w_depth, void* scratch, size_t scratch_bytes, float* dL_dcolor, float* dL_dinvdepth,
-                         float* loss, void* stream);
+                         const float* prior, const float* mask, const float* alpha_mask, int32_t clamp01, int32_t width,
+                         int32_t height, float lambda_dssim, float w_depth, void* scratch, size_t scratch_bytes,
+                         float* dL_dcolor, float* dL_dinvdepth, float* loss, void* stream);
 
 /* Visibility-sparse Adam: the kernel under `SparseGaussianAdam.step(visibility, N)`, which the reference uses when the
  * rasterizer package exports that class (/root/reference/train.py:47-52, 332-334; scene/gaussian_model.py:25-28,

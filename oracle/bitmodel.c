@@ -125,11 +125,13 @@ int64_t bm_preprocess(int64_t P, const float* means, const float* scales, float 
     float c0 = d3(M1[0], v1[0], M1[1], v1[1], M1[2], v1[2]);
     float a = a0 + 0.3f, c = c0 + 0.3f;
     float det = fmaf(a, c, -(b * b));
-    if (det == 0.0f) continue;
+    if (det == 0.0f || !(det == det)) continue; /* non-finite covariance: culled (pdgs_math.cuh forward_geometry) */
     float mid = 0.5f * (a + c);
     float disc = sqrtf(fmaxf(0.1f, fmaf(mid, mid, -det)));
     float lam = fmaxf(mid + disc, mid - disc);
+    if (!(lam == lam)) continue;
     int rad = trunc_i(ceilf(3.0f * sqrtf(lam)));
+    if (rad <= 0) continue;
     float px = pix_of_ndc(nx, W), py = pix_of_ndc(ny, H);
     float rf = (float)rad;
     int x0 = clampi(trunc_i((px - rf) / 16.0f), 0, gx);
@@ -144,8 +146,8 @@ int64_t bm_preprocess(int64_t P, const float* means, const float* scales, float 
     xy[2 * i] = px;
     xy[2 * i + 1] = py;
     memcpy(&depth_bits[i], &vz, 4);
+    if (!(x1 > x0 && y1 > y0)) continue;
     int area = (x1 - x0) * (y1 - y0);
-    if (area == 0) continue;
     radii[i] = rad;
     tiles[i] = (uint32_t)area;
     total += area;

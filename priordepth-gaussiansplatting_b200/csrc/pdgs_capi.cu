@@ -324,15 +324,16 @@ int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, 
 }
 
 int pdgs_image_loss(PdgsHandle* h, const float* color, const float* target, const float* invdepth,
-                    const float* prior, const float* mask, int32_t width, int32_t height, float w_color,
-                    float w_depth, float* dL_dcolor, float* dL_dinvdepth, float* loss, void* stream) {
+                    const float* prior, const float* mask, const float* alpha_mask, int32_t clamp01, int32_t width,
+                    int32_t height, float w_color, float w_depth, float* dL_dcolor, float* dL_dinvdepth, float* loss,
+                    void* stream) {
   if (!h || !color || !target || !dL_dcolor || !loss || width <= 0 || height <= 0)
     return fail(PDGS_E_INVALID, "pdgs_image_loss: bad argument");
   if (prior && (!invdepth || !dL_dinvdepth)) return fail(PDGS_E_INVALID, "pdgs_image_loss: prior given without invdepth / dL_dinvdepth");
   cudaStream_t s = (cudaStream_t)stream;
   StageTimer t(h, PDGS_STAGE_LOSS, s);
-  PD_CUDA(launch_image_loss(color, target, invdepth, prior, mask, width, height, w_color, w_depth, dL_dcolor,
-                            dL_dinvdepth, loss, s));
+  PD_CUDA(launch_image_loss(color, target, invdepth, prior, mask, alpha_mask, clamp01 ? 1 : 0, width, height, w_color,
+                            w_depth, dL_dcolor, dL_dinvdepth, loss, s));
   return PDGS_OK;
 }
 
@@ -353,7 +354,7 @@ int pdgs_ssim_forward(PdgsHandle* h, float C1, float C2, const float* img1, cons
   StageTimer t(h, PDGS_STAGE_LOSS, s);
   if (ssim_sum) PD_CUDA(cudaMemsetAsync(h->dsums, 0, 16, s));
   PD_CUDA(launch_ssim_forward(C1, C2, img1, img2, planes, width, height, ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12,
-                              ssim_sum ? h->dsums : nullptr, 0, s));
+                              ssim_sum ? h->dsums : nullptr, 0, nullptr, 0, s));
   if (ssim_sum && planes > 0) PD_CUDA(launch_ssim_finalize(h->dsums, 1.0, ssim_sum, nullptr, s));
   return PDGS_OK;
 }
@@ -368,14 +369,14 @@ int pdgs_ssim_backward(PdgsHandle* h, const float* img1, const float* img2, cons
   cudaStream_t s = (cudaStream_t)stream;
   StageTimer t(h, PDGS_STAGE_LOSS, s);
   PD_CUDA(launch_ssim_backward(img1, img2, dL_dmap, dL_dmap_uniform, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, planes, width,
-                               height, 0.f, dL_dimg1, nullptr, 0.0, nullptr, nullptr, s));
+                               height, 0.f, dL_dimg1, nullptr, 0.0, nullptr, nullptr, nullptr, 0, s));
   return PDGS_OK;
 }
 
 int pdgs_image_loss_ssim(PdgsHandle* h, const float* color, const float* target, const float* invdepth,
-                         const float* prior, const float* mask, int32_t width, int32_t height, float lambda_dssim,
-                         float w_depth, void* scratch, size_t scratch_bytes, float* dL_dcolor, float* dL_dinvdepth,
-                         float* loss, void* stream) {
+                         const float* prior, const float* mask, const float* alpha_mask, int32_t clamp01, int32_t width,
+                         int32_t height, float lambda_dssim, float w_depth, void* scratch, size_t scratch_bytes,
+                         float* dL_dcolor, float* dL_dinvdepth, float* loss, void* stream) {
   if (!h || !color || !target || !dL_dcolor || !loss || width <= 0 || height <= 0)
     return fail(PDGS_E_INVALID, "pdgs_image_loss_ssim: bad argument");
   if (prior && (!invdepth || !dL_dinvdepth))
@@ -391,14 +392,16 @@ int pdgs_image_loss_ssim(PdgsHandle* h, const float* color, const float* target,
   const float inv_n = 1.0f / (float)n;
   // partial maps into the scratch; sum of the SSIM map and sum |color - target| accumulated in double
   PD_CUDA(cudaMemsetAsync(h->dsums, 0, 16, s));
+  const int cl = clamp01 ? 1 : 0;
   PD_CUDA(launch_ssim_forward(0.01f * 0.01f, 0.03f * 0.03f, color, target, 3, width, height, nullptr, d_mu, d_s1, d_s12,
-                              h->dsums, 1, s));
+                              h->dsums, 1, alpha_mask, cl, s));
   // d/dcolor [(1 - lambda) mean|c - t| + lambda (1 - mean ssim)]; its first block folds the sums into loss[2], loss[0]
   PD_CUDA(launch_ssim_backward(color, target, nullptr, -lambda_dssim * inv_n, d_mu, d_s1, d_s12, 3, width, height,
-                               (1.0f - lambda_dssim) * inv_n, dL_dcolor, h->dsums, 1.0 / (double)n, loss + 2, loss + 0, s));
+                               (1.0f - lambda_dssim) * inv_n, dL_dcolor, h->dsums, 1.0 / (double)n, loss + 2, loss + 0,
+                               alpha_mask, cl, s));
   if (prior)
-    PD_CUDA(launch_image_loss(nullptr, nullptr, invdepth, prior, mask, width, height, 0.f, w_depth, nullptr, dL_dinvdepth,
-                              loss, s));
+    PD_CUDA(launch_image_loss(nullptr, nullptr, invdepth, prior, mask, nullptr, 0, width, height, 0.f, w_depth, nullptr,
+                              dL_dinvdepth, loss, s));
   return PDGS_OK;
 }
 

@@ -220,18 +220,19 @@ cudaError_t launch_sh_backward_views(const float* means3D, const float* shs, con
                                      int64_t P, int M, int sh_degree, const float* campos_views, const float* color_grads,
                                      int n_views, float* grad_shs, float* grad_dc, float* grad_rest, float* grad_means3D,
                                      int accumulate, cudaStream_t s);
+// alpha / clamp01: the loss sees clamp(color, 0, 1) * alpha (alpha: one [H*W] plane or NULL), see pdgs_loss.cu
 cudaError_t launch_image_loss(const float* color, const float* target, const float* invdepth, const float* prior,
-                              const float* mask, int W, int H, float w_color, float w_depth, float* dL_dcolor,
-                              float* dL_dinvdepth, float* loss, cudaStream_t s);
+                              const float* mask, const float* alpha, int clamp01, int W, int H, float w_color,
+                              float w_depth, float* dL_dcolor, float* dL_dinvdepth, float* loss, cudaStream_t s);
 // SSIM (pdgs_ssim.cu).  sums: device double[2] zeroed by the caller (sum of the map, sum |img1 - img2|)
 cudaError_t launch_ssim_forward(float C1, float C2, const float* img1, const float* img2, int planes, int W, int H,
                                 float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12, double* sums,
-                                int want_l1, cudaStream_t s);
+                                int want_l1, const float* alpha, int clamp01, cudaStream_t s);
 cudaError_t launch_ssim_finalize(const double* sums, double scale, float* out_ssim, float* out_l1, cudaStream_t s);
 cudaError_t launch_ssim_backward(const float* img1, const float* img2, const float* dL_dmap, float dL_uniform,
                                  const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, int planes, int W,
                                  int H, float l1_weight, float* dL_dimg1, const double* fin_sums, double fin_scale,
-                                 float* fin_ssim, float* fin_l1, cudaStream_t s);
+                                 float* fin_ssim, float* fin_l1, const float* alpha, int clamp01, cudaStream_t s);
 // Visibility-sparse Adam (pdgs_optim.cu).  One group = one parameter tensor [N, M] with its gradient and moments.
 constexpr int ADAM_MAX_GROUPS = 8;
 struct AdamGroup {

@@ -9,8 +9,8 @@
 // pixel centres) is written with explicit round-to-nearest intrinsics in one
 // fixed ("canonical") operation order, documented in DESIGN.md, so that the
 // fp32 bit-model under oracle/ can reproduce it bit for bit.  The functions are
-// __host__ __device__ so the unit tests can run the very same source on the CPU
-// (tests/hostmath); the product never executes the host instantiation.
+// __host__ __device__ so the same source can be instantiated on the host; the
+// product never executes the host instantiation.
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
@@ -195,7 +195,10 @@ PD_HD bool forward_geometry(const Camera& cam, float mx, float my, float mz, con
   const float det0 = PD_FMA(e.a0, e.c0, -PD_MUL(e.b, e.b));
   const float a = PD_ADD(e.a0, DILATION), c = PD_ADD(e.c0, DILATION);
   const float det = PD_FMA(a, c, -PD_MUL(e.b, e.b));
-  if (det == 0.0f) return false;
+  // det == 0 culls as upstream does; a non-finite covariance (NaN scale / rotation, exp() overflow of a raw scale) is
+  // culled too: upstream's (int)NaN == 0 radius gives a zero-area rect there, here the same Gaussian must not reach
+  // the binning with an inverted rect
+  if (det == 0.0f || !(det == det)) return false;
   g.h = cam.antialiasing ? PD_SQRT(fmaxf(AA_FLOOR, PD_DIV(det0, det))) : 1.0f;
   const float det_inv = PD_DIV(1.0f, det);
   g.conA = PD_MUL(c, det_inv);
@@ -204,11 +207,13 @@ PD_HD bool forward_geometry(const Camera& cam, float mx, float my, float mz, con
   const float mid = PD_MUL(0.5f, PD_ADD(a, c));
   const float disc = PD_SQRT(fmaxf(0.1f, PD_FMA(mid, mid, -det)));
   const float lam = fmaxf(PD_ADD(mid, disc), PD_SUB(mid, disc));
+  if (!(lam == lam)) return false;
   const int radius = f2i_trunc_safe(ceilf(PD_MUL(3.0f, PD_SQRT(lam))));
+  if (radius <= 0) return false;
   g.px = ndc2pix(ndcx, cam.W);
   g.py = ndc2pix(ndcy, cam.H);
   tile_rect(g.px, g.py, radius, cam.grid_x, cam.grid_y, g.rx0, g.ry0, g.rx1, g.ry1);
-  if ((g.rx1 - g.rx0) * (g.ry1 - g.ry0) == 0) return false;
+  if (!(g.rx1 > g.rx0 && g.ry1 > g.ry0)) return false;  // empty (or, for a NaN centre, inverted) rect
   g.radius = radius;
   g.depth = pvz;
   return true;

@@ -63,10 +63,15 @@ __device__ __forceinline__ float block_sum256(float v, float* s_red) {
 // Stage NQ planes' halo (SROWS x SPITCH, zero outside the image) around the tile at (tx0, ty0): dst[q][r][c] =
 // src[q] * (mul ? mul : mul_uniform).  vec: the image rows can be read as aligned float4 (W % 4 == 0 and 16-byte
 // aligned planes); all loads of a thread are issued before the first store.
-template <int NQ>
+// FIRST (loss path, src[0] = the rendered image): the multiplier applies to plane 0 only, after an optional clamp to
+// [0, 1] -- the caller-side `rendered_image.clamp(0, 1)` and `image *= alpha_mask` of the reference
+// (gaussian_renderer/__init__.py:121, train.py:148-150).
+__device__ __forceinline__ float clamp01f(float v) { return fminf(fmaxf(v, 0.f), 1.f); }
+
+template <int NQ, bool FIRST = false>
 __device__ __forceinline__ void stage_halo(float (*dst)[SROWS][SPITCH], const float* const (&src)[NQ],
                                            const float* __restrict__ mul, float mul_uniform, int W, int H, int tx0,
-                                           int ty0, bool vec) {
+                                           int ty0, bool vec, bool clamp0 = false) {
   constexpr int ITEMS = SROWS * (SPITCH / 4);  // 504 float4 per plane
   constexpr int ROUNDS = (ITEMS + STHREADS - 1) / STHREADS;
   float4 v[ROUNDS][NQ];
@@ -85,7 +90,9 @@ __device__ __forceinline__ void stage_halo(float (*dst)[SROWS][SPITCH], const fl
       for (int q = 0; q < NQ; ++q) {
         float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
         if (ok) t = __ldg(reinterpret_cast<const float4*>(src[q] + p));
-        v[rd][q] = make_float4(t.x * m.x, t.y * m.y, t.z * m.z, t.w * m.w);
+        if (FIRST && q == 0 && clamp0) t = make_float4(clamp01f(t.x), clamp01f(t.y), clamp01f(t.z), clamp01f(t.w));
+        if (FIRST && q != 0) v[rd][q] = t;
+        else v[rd][q] = make_float4(t.x * m.x, t.y * m.y, t.z * m.z, t.w * m.w);
       }
     } else {
 #pragma unroll
@@ -97,7 +104,9 @@ __device__ __forceinline__ void stage_halo(float (*dst)[SROWS][SPITCH], const fl
           e[i] = 0.f;
           if (row_ok && x >= 0 && x < W) {
             const size_t p = (size_t)y * W + x;
-            e[i] = __ldg(src[q] + p) * (mul ? __ldg(mul + p) : mul_uniform);
+            float t = __ldg(src[q] + p);
+            if (FIRST && q == 0 && clamp0) t = clamp01f(t);
+            e[i] = (FIRST && q != 0) ? t : t * (mul ? __ldg(mul + p) : mul_uniform);
           }
         }
         v[rd][q] = make_float4(e[0], e[1], e[2], e[3]);
@@ -150,14 +159,17 @@ __global__ void __launch_bounds__(STHREADS) ssim_forward_kernel(float C1, float 
                                                                 float* __restrict__ dm_dmu1,
                                                                 float* __restrict__ dm_dsigma1_sq,
                                                                 float* __restrict__ dm_dsigma12,
-                                                                double* __restrict__ sums, int want_l1) {
+                                                                double* __restrict__ sums, int want_l1,
+                                                                const float* __restrict__ alpha, int clamp01) {
   extern __shared__ __align__(16) unsigned char ssim_smem[];
   SsimFwdSmem& sm = *reinterpret_cast<SsimFwdSmem*>(ssim_smem);
   const size_t plane = (size_t)blockIdx.z * W * H;
   const int tx0 = blockIdx.x * ST, ty0 = blockIdx.y * ST;
   {
     const float* const src[2] = {img1 + plane, img2 + plane};
-    stage_halo<2>(sm.in, src, nullptr, 1.f, W, H, tx0, ty0, vec != 0);
+    // loss path: img1 is staged as clamp(img1, 0, 1) * alpha (one alpha plane for all colour planes)
+    if (alpha || clamp01) stage_halo<2, true>(sm.in, src, alpha, 1.f, W, H, tx0, ty0, vec != 0, clamp01 != 0);
+    else stage_halo<2>(sm.in, src, nullptr, 1.f, W, H, tx0, ty0, vec != 0);
   }
   __syncthreads();
   // horizontal pass: item = (row r, group of 4 output columns); the products are formed once per staged value
@@ -230,8 +242,9 @@ __global__ void __launch_bounds__(STHREADS) ssim_forward_kernel(float C1, float 
 
 // out[i] += scale * sums[i] (float accumulators of the C ABI); one thread
 __global__ void ssim_finalize_kernel(const double* __restrict__ sums, double scale, float* out0, float* out1) {
-  if (out0) *out0 += (float)(sums[0] * scale);
-  if (out1) *out1 += (float)(sums[1] * scale);
+  // atomic: several views (streams) may fold into the same accumulators concurrently
+  if (out0) atomicAdd(out0, (float)(sums[0] * scale));
+  if (out1) atomicAdd(out1, (float)(sums[1] * scale));
 }
 
 struct SsimBwdSmem {
@@ -248,14 +261,15 @@ __global__ void __launch_bounds__(STHREADS) ssim_backward_kernel(const float* __
                                                                  const float* __restrict__ dm_dsigma12, int W, int H,
                                                                  int vec, float l1_weight, float* __restrict__ dL_dimg1,
                                                                  const double* __restrict__ fin_sums, double fin_scale,
-                                                                 float* fin_ssim, float* fin_l1) {
+                                                                 float* fin_ssim, float* fin_l1,
+                                                                 const float* __restrict__ alpha, int clamp01) {
   extern __shared__ __align__(16) unsigned char ssim_smem[];
   SsimBwdSmem& sm = *reinterpret_cast<SsimBwdSmem*>(ssim_smem);
   const size_t plane = (size_t)blockIdx.z * W * H;
   const int tx0 = blockIdx.x * ST, ty0 = blockIdx.y * ST;
   if (fin_sums && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
-    *fin_ssim += (float)(fin_sums[0] * fin_scale);
-    *fin_l1 += (float)(fin_sums[1] * fin_scale);
+    atomicAdd(fin_ssim, (float)(fin_sums[0] * fin_scale));  // atomic: the accumulators are shared by concurrent views
+    atomicAdd(fin_l1, (float)(fin_sums[1] * fin_scale));
   }
   {
     const float* const src[3] = {dm_dmu1 + plane, dm_dsigma1_sq + plane, dm_dsigma12 + plane};
@@ -286,13 +300,19 @@ __global__ void __launch_bounds__(STHREADS) ssim_backward_kernel(const float* __
     const int py = ty0 + 4 * yb + j;
     if (px < W && py < H) {
       const size_t p = plane + (size_t)py * W + px;
-      const float a = __ldg(img1 + p), b = __ldg(img2 + p);
+      const float raw = __ldg(img1 + p), b = __ldg(img2 + p);
+      // loss path: the image the losses saw is a = clamp(raw, 0, 1) * alpha; its cotangent reaches raw through alpha
+      // where 0 <= raw <= 1 and not at all elsewhere (torch.clamp's backward)
+      const float am = alpha ? __ldg(alpha + (size_t)py * W + px) : 1.f;
+      const float a = (clamp01 ? clamp01f(raw) : raw) * am;
       // dL/da(p) = sum_q w(q-p) dL/dm(q) [dm/dmu1(q) + 2 a(p) dm/dsigma1_sq(q) + b(p) dm/dsigma12(q)]
       float d = acc[0][j] + 2.f * a * acc[1][j] + b * acc[2][j];
       if (l1_weight != 0.f) {
         const float e = a - b;
         d += l1_weight * ((e > 0.f) ? 1.f : ((e < 0.f) ? -1.f : 0.f));
       }
+      d *= am;
+      if (clamp01 && !(raw >= 0.f && raw <= 1.f)) d = 0.f;
       dL_dimg1[p] = d;
     }
   }
@@ -322,15 +342,15 @@ bool rows_vectorizable(int W, std::initializer_list<const void*> ptrs) {
 // sums: device double[2], zeroed by the caller on the same stream (sum of the map, sum |img1 - img2| when want_l1)
 cudaError_t launch_ssim_forward(float C1, float C2, const float* img1, const float* img2, int planes, int W, int H,
                                 float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12, double* sums,
-                                int want_l1, cudaStream_t s) {
+                                int want_l1, const float* alpha, int clamp01, cudaStream_t s) {
   if (planes <= 0 || W <= 0 || H <= 0) return cudaSuccess;
   static thread_local int dev_f = -1;
   cudaError_t e = opt_in_smem((const void*)ssim_forward_kernel, sizeof(SsimFwdSmem), &dev_f);
   if (e != cudaSuccess) return e;
-  const int vec = rows_vectorizable(W, {img1, img2}) && (((size_t)W * H) % 4 == 0);
+  const int vec = rows_vectorizable(W, {img1, img2, alpha}) && (((size_t)W * H) % 4 == 0);
   dim3 grid((W + ST - 1) / ST, (H + ST - 1) / ST, planes);
   ssim_forward_kernel<<<grid, STHREADS, sizeof(SsimFwdSmem), s>>>(C1, C2, img1, img2, W, H, vec, ssim_map, dm_dmu1,
-                                                                  dm_dsigma1_sq, dm_dsigma12, sums, want_l1);
+                                                                  dm_dsigma1_sq, dm_dsigma12, sums, want_l1, alpha, clamp01);
   return cudaGetLastError();
 }
 
@@ -342,7 +362,7 @@ cudaError_t launch_ssim_finalize(const double* sums, double scale, float* out_ss
 cudaError_t launch_ssim_backward(const float* img1, const float* img2, const float* dL_dmap, float dL_uniform,
                                  const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, int planes, int W,
                                  int H, float l1_weight, float* dL_dimg1, const double* fin_sums, double fin_scale,
-                                 float* fin_ssim, float* fin_l1, cudaStream_t s) {
+                                 float* fin_ssim, float* fin_l1, const float* alpha, int clamp01, cudaStream_t s) {
   if (planes <= 0 || W <= 0 || H <= 0) return cudaSuccess;
   static thread_local int dev_b = -1;
   cudaError_t e = opt_in_smem((const void*)ssim_backward_kernel, sizeof(SsimBwdSmem), &dev_b);
@@ -351,7 +371,7 @@ cudaError_t launch_ssim_backward(const float* img1, const float* img2, const flo
   dim3 grid((W + ST - 1) / ST, (H + ST - 1) / ST, planes);
   ssim_backward_kernel<<<grid, STHREADS, sizeof(SsimBwdSmem), s>>>(img1, img2, dL_dmap, dL_uniform, dm_dmu1, dm_dsigma1_sq,
                                                                    dm_dsigma12, W, H, vec, l1_weight, dL_dimg1, fin_sums,
-                                                                   fin_scale, fin_ssim, fin_l1);
+                                                                   fin_scale, fin_ssim, fin_l1, alpha, clamp01);
   return cudaGetLastError();
 }
 

@@ -69,12 +69,13 @@ SYMBOLS = {
     "pdgs_destroy": (C.c_int, [vp]),
     "pdgs_set_stage_timing": (C.c_int, [vp, C.c_int32]),
     "pdgs_stage_times": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_int32]),
-    "pdgs_image_loss": (C.c_int, [vp, vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_float, C.c_float, vp, vp, vp, vp]),
+    "pdgs_image_loss": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, vp, vp,
+                                  vp, vp]),
     "pdgs_ssim_forward": (C.c_int, [vp, C.c_float, C.c_float, vp, vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),
     "pdgs_ssim_backward": (C.c_int, [vp, vp, vp, vp, C.c_float, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, vp, vp]),
     "pdgs_ssim_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
-    "pdgs_image_loss_ssim": (C.c_int, [vp, vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_float, C.c_float, vp, C.c_size_t,
-                                       vp, vp, vp, vp]),
+    "pdgs_image_loss_ssim": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, vp,
+                                       C.c_size_t, vp, vp, vp, vp]),
     "pdgs_geom_bytes": (C.c_size_t, [C.c_int64]),
     "pdgs_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "pdgs_binning_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),

@@ -10,6 +10,7 @@ libpdgs.so.  Argument order and return tuples of `rasterize_gaussians` /
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from typing import Optional
 
 import torch
@@ -18,11 +19,18 @@ from . import _lib as L
 
 # per-device speculative capacity of the binning buffer (pairs); follows the last pair count
 _capacity_hint = {}
-# number of kernels of ours launched by the last forward / backward (for bench.py's gpu_launches)
-LAUNCHES_FORWARD = 0
-LAUNCHES_BACKWARD = 0
-LAUNCHES_SH_BWD = 0
-LAUNCHES_LOSS = 0
+
+
+class _Launches(threading.local):
+    """Kernels of ours launched by the calling thread's last forward / backward / loss / SH-backward call (for
+    bench.py's gpu_launches).  Thread-local: the view-parallel lanes call in from several host threads."""
+    forward = 0
+    backward = 0
+    sh_bwd = 0
+    loss = 0
+
+
+LAUNCHES = _Launches()
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -106,9 +114,12 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
     `sh` is features_rest [P,M-1,3] (the pair render() passes when separate_sh is set,
     /root/reference/gaussian_renderer/__init__.py:82-101); `raw_params` = opacities / scales / rotations are the
     pre-activation parameters and sigmoid / exp / normalize run inside the preprocess kernel."""
-    global LAUNCHES_FORWARD
     if means3D.dim() != 2 or means3D.shape[1] != 3:
         raise L.PdgsError("means3D must have dimensions (num_points, 3)")
+    if prefiltered:
+        # upstream traps the kernel when a point marked as prefiltered fails the frustum test; the reference always
+        # passes False (/root/reference/gaussian_renderer/__init__.py:47).  Reject instead of silently ignoring it.
+        raise L.PdgsError("prefiltered=True is not supported: this rasterizer always culls by itself (pass False)")
     lib = L.lib()
     dev = means3D.device
     if not means3D.is_cuda:
@@ -170,7 +181,7 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
         if binning is None:
             binning = torch.empty(0, **u8)
         binning._pdgs_capacity = cap
-        LAUNCHES_FORWARD = launches
+        LAUNCHES.forward = launches
     return int(R.value), color, radii, geom, binning, image, invdepth
 
 
@@ -187,7 +198,6 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
     the dict has "overwrite": True); "densify_grad_accum" / "densify_denom" / "max_radii2D" receive the statistics.
     dc / raw_params: as in rasterize_gaussians; with `dc` the tuple gains a ninth element grad_dc[P,1,3] and grad_sh is
     the gradient of features_rest; with raw_params the opacity / scale / rotation gradients are w.r.t. the raw tensors."""
-    global LAUNCHES_BACKWARD
     lib = L.lib()
     dev = means3D.device
     P = means3D.shape[0]
@@ -261,7 +271,7 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
             L.check(lib.pdgs_backward(h, C.byref(sc), C.byref(cam), C.byref(st), _ptr(radii), int(num_rendered),
                                       _ptr(grad_out_color), _ptr(grad_out_invdepth), _ptr(scratch), scratch.numel(),
                                       C.byref(g), stream), "pdgs_backward")
-            LAUNCHES_BACKWARD = 2 if num_rendered > 0 else 1
+            LAUNCHES.backward = 2 if num_rendered > 0 else 1
     if dc is not None:
         return dmeans2D, dcolors, dopac, dmeans3D, dcov, dsh, dscales, drots, ddc
     return dmeans2D, dcolors, dopac, dmeans3D, dcov, dsh, dscales, drots
@@ -271,7 +281,6 @@ def sh_backward_views_split(means3D, dc, rest, sh_degree, campos_views, color_gr
                             accumulate=True):
     """sh_backward_views for a scene given as features_dc [P,1,3] / features_rest [P,M-1,3]
     (C ABI pdgs_sh_backward_views_split)."""
-    global LAUNCHES_SH_BWD
     lib = L.lib()
     dev = means3D.device
     if not means3D.is_cuda:
@@ -288,7 +297,7 @@ def sh_backward_views_split(means3D, dc, rest, sh_degree, campos_views, color_gr
         L.check(lib.pdgs_sh_backward_views_split(h, C.byref(sc), int(sh_degree), _ptr(campos_views), _ptr(color_grads), V,
                                                  _ptr(grad_dc), _ptr(grad_rest), _ptr(grad_means3D), int(bool(accumulate)),
                                                  stream), "pdgs_sh_backward_views_split")
-        LAUNCHES_SH_BWD = (V + 255) // 256
+        LAUNCHES.sh_bwd = (V + 255) // 256
     return grad_dc, grad_rest, grad_means3D
 
 
@@ -296,7 +305,6 @@ def sh_backward_views(means3D, sh, sh_degree, campos_views, color_grads, grad_sh
     """SH part of the backward for a batch of views at once (C ABI pdgs_sh_backward_views): reads `color_grads`
     [V,P,3] (what backward left in accumulate_into["color_grad_view"] per view) and `campos_views` [V,3]; writes
     or accumulates grad_shs [P,M,3] and adds the view-direction term to grad_means3D [P,3]."""
-    global LAUNCHES_SH_BWD
     lib = L.lib()
     dev = means3D.device
     if not means3D.is_cuda:
@@ -313,15 +321,17 @@ def sh_backward_views(means3D, sh, sh_degree, campos_views, color_grads, grad_sh
         L.check(lib.pdgs_sh_backward_views(h, C.byref(sc), int(sh_degree), _ptr(campos_views), _ptr(color_grads), V,
                                            _ptr(grad_shs), _ptr(grad_means3D), int(bool(accumulate)), stream),
                 "pdgs_sh_backward_views")
-        LAUNCHES_SH_BWD = (V + 255) // 256
+        LAUNCHES.sh_bwd = (V + 255) // 256
     return grad_shs, grad_means3D
 
 
-def image_loss(color, target, invdepth=None, prior=None, mask=None, w_color=1.0, w_depth=0.0, loss_acc=None):
+def image_loss(color, target, invdepth=None, prior=None, mask=None, w_color=1.0, w_depth=0.0, loss_acc=None,
+               clamp=False, alpha_mask=None):
     """One-pass image loss + cotangents (C ABI pdgs_image_loss; the torch ops at
     /root/reference/train.py:153,174).  -> (dL_dcolor[3,H,W], dL_dinvdepth[1,H,W] or None, loss_acc[2]);
-    loss_acc (device float[2]: mean L1, mean masked depth L1) is accumulated into when given."""
-    global LAUNCHES_LOSS
+    loss_acc (device float[2]: mean L1, mean masked depth L1) is accumulated into when given.
+    clamp / alpha_mask: the loss is taken on clamp(color, 0, 1) * alpha_mask as the reference's caller does
+    (gaussian_renderer/__init__.py:121, train.py:148-150) and dL_dcolor is w.r.t. the raw `color`."""
     lib = L.lib()
     dev = color.device
     if not color.is_cuda:
@@ -332,6 +342,7 @@ def image_loss(color, target, invdepth=None, prior=None, mask=None, w_color=1.0,
     if target is None or target.numel() != color.numel():
         raise L.PdgsError("target must have the shape of color")
     invdepth, prior, mask = _f32c(invdepth, "invdepth", dev), _f32c(prior, "prior", dev), _f32c(mask, "mask", dev)
+    alpha_mask = _alpha_plane(alpha_mask, H, W, dev)
     with torch.cuda.device(dev):
         h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
         stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
@@ -339,19 +350,29 @@ def image_loss(color, target, invdepth=None, prior=None, mask=None, w_color=1.0,
         ddepth = torch.empty(1, H, W, dtype=torch.float32, device=dev) if prior is not None else None
         if loss_acc is None:
             loss_acc = torch.zeros(2, dtype=torch.float32, device=dev)
-        L.check(lib.pdgs_image_loss(h, _ptr(color), _ptr(target), _ptr(invdepth), _ptr(prior), _ptr(mask), W, H,
-                                    float(w_color), float(w_depth), _ptr(dcolor), _ptr(ddepth), _ptr(loss_acc), stream),
-                "pdgs_image_loss")
-        LAUNCHES_LOSS = 1
+        L.check(lib.pdgs_image_loss(h, _ptr(color), _ptr(target), _ptr(invdepth), _ptr(prior), _ptr(mask),
+                                    _ptr(alpha_mask), int(bool(clamp)), W, H, float(w_color), float(w_depth), _ptr(dcolor),
+                                    _ptr(ddepth), _ptr(loss_acc), stream), "pdgs_image_loss")
+        LAUNCHES.loss = 1
     return dcolor, ddepth, loss_acc
 
 
+def _alpha_plane(alpha_mask, H, W, dev):
+    """alpha_mask [1,H,W] / [H,W] (the camera's alpha_mask, /root/reference/train.py:148-150) as one fp32 plane."""
+    alpha_mask = _f32c(alpha_mask, "alpha_mask", dev)
+    if alpha_mask is not None and alpha_mask.numel() != H * W:
+        raise L.PdgsError("alpha_mask must hold one value per pixel ([1,H,W] or [H,W])")
+    return alpha_mask
+
+
 def image_loss_ssim(color, target, invdepth=None, prior=None, mask=None, lambda_dssim=0.2, w_depth=0.0, loss_acc=None,
-                    scratch=None):
+                    scratch=None, clamp=True, alpha_mask=None):
     """The reference's training loss and its cotangents (C ABI pdgs_image_loss_ssim; the torch ops at
-    /root/reference/train.py:153-159 `(1-l)*l1 + l*(1-ssim)` and :174 the depth-prior term).
+    /root/reference/train.py:148-159 on the image render() returns, i.e. `image = render.clamp(0, 1)`
+    (gaussian_renderer/__init__.py:121), `image *= alpha_mask`, `(1-l)*l1 + l*(1-ssim)`, and :174 the depth-prior
+    term).  `color` is the RAW rasterizer output; clamp=True (default) applies the clamp inside the kernels and
+    dL_dcolor is zero where color is outside [0, 1].
     -> (dL_dcolor[3,H,W], dL_dinvdepth[1,H,W] or None, loss_acc[3] = mean L1, mean masked depth L1, mean SSIM)."""
-    global LAUNCHES_LOSS
     lib = L.lib()
     dev = color.device
     if not color.is_cuda:
@@ -362,6 +383,7 @@ def image_loss_ssim(color, target, invdepth=None, prior=None, mask=None, lambda_
     if target is None or target.numel() != color.numel() or color.numel() != 3 * H * W:
         raise L.PdgsError("color and target must both be [3,H,W]")
     invdepth, prior, mask = _f32c(invdepth, "invdepth", dev), _f32c(prior, "prior", dev), _f32c(mask, "mask", dev)
+    alpha_mask = _alpha_plane(alpha_mask, H, W, dev)
     with torch.cuda.device(dev):
         h = L.handle(dev.index if dev.index is not None else torch.cuda.current_device())
         stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
@@ -372,10 +394,11 @@ def image_loss_ssim(color, target, invdepth=None, prior=None, mask=None, lambda_
         ddepth = torch.empty(1, H, W, dtype=torch.float32, device=dev) if prior is not None else None
         if loss_acc is None:
             loss_acc = torch.zeros(3, dtype=torch.float32, device=dev)
-        L.check(lib.pdgs_image_loss_ssim(h, _ptr(color), _ptr(target), _ptr(invdepth), _ptr(prior), _ptr(mask), W, H,
-                                         float(lambda_dssim), float(w_depth), _ptr(scratch), scratch.numel(), _ptr(dcolor),
-                                         _ptr(ddepth), _ptr(loss_acc), stream), "pdgs_image_loss_ssim")
-        LAUNCHES_LOSS = 3 if prior is not None else 2
+        L.check(lib.pdgs_image_loss_ssim(h, _ptr(color), _ptr(target), _ptr(invdepth), _ptr(prior), _ptr(mask),
+                                         _ptr(alpha_mask), int(bool(clamp)), W, H, float(lambda_dssim), float(w_depth),
+                                         _ptr(scratch), scratch.numel(), _ptr(dcolor), _ptr(ddepth), _ptr(loss_acc), stream),
+                "pdgs_image_loss_ssim")
+        LAUNCHES.loss = 3 if prior is not None else 2
     return dcolor, ddepth, loss_acc
 
 

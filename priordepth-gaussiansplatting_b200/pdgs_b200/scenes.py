@@ -141,7 +141,7 @@ def orbit_scene(name: str, k: int, P: int, W: int, H: int, mu_px: float, n_views
 
 
 # mu_px calibrated with the fp32 bit-model to the duplication targets of SURVEY 8d
-# (R/P: C1 ~ 8, C2 ~ 2.5, C3 ~ 3, C4 ~ 3, C5 ~ 16); see tests/test_scenes.py.
+# (R/P: C1 ~ 8, C2 ~ 2.5, C3 ~ 3, C4 ~ 3, C5 ~ 16); tests/test_gpu_fullsize.py prints the achieved ratios.
 CONFIGS = {
     "C1": dict(k=1, P=10_000, W=256, H=256, mu_px=2.978, kind="cam"),
     "C2": dict(k=2, P=5_800_000, W=1297, H=840, mu_px=1.065, kind="cam"),

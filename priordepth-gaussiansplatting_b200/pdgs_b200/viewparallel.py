@@ -104,9 +104,11 @@ class GradBuffer:
 
 
 def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, mask, w_depth, acc: Dict, loss_acc,
-                       lambda_dssim: float = 0.0, scratch: Optional[Dict] = None):
+                       lambda_dssim: float = 0.0, scratch: Optional[Dict] = None, clamp: bool = True, alpha_mask=None):
     """forward -> image loss -> backward (accumulating) of ONE view on the CUDA library.  lambda_dssim > 0 selects
-    the reference's training loss (1-l)*L1 + l*(1-SSIM) (/root/reference/train.py:153-159), else plain L1."""
+    the reference's training loss (1-l)*L1 + l*(1-SSIM) (/root/reference/train.py:153-159), else plain L1.  clamp /
+    alpha_mask: the loss sees clamp(render, 0, 1) * alpha_mask like the reference's caller
+    (gaussian_renderer/__init__.py:121, train.py:148-150); the clamp and its backward run inside the loss kernels."""
     from . import rasterizer as rz
     empty = torch.empty(0, device=gaussians["means3D"].device)
     # split SH (features_dc / features_rest) and raw parameters: SURVEY 8(f) rank 2, see rz.rasterize_gaussians
@@ -119,7 +121,7 @@ def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, ma
         gaussians["rotations"], rs.scale_modifier, empty, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
         rs.image_height, rs.image_width, empty if shs is None else shs, rs.sh_degree, rs.campos, False, rs.antialiasing,
         rs.debug, dc=dc, raw_params=raw)
-    launches = rz.LAUNCHES_FORWARD
+    launches = rz.LAUNCHES.forward
     use_depth = prior is not None and w_depth != 0.0
     if lambda_dssim > 0.0:
         buf = None if scratch is None else scratch.get("ssim")
@@ -129,17 +131,19 @@ def _cuda_view_backend(gaussians: Dict[str, torch.Tensor], rs, target, prior, ma
             if scratch is not None:
                 scratch["ssim"] = buf
         dcolor, ddepth, _ = rz.image_loss_ssim(color, target, invd if use_depth else None, prior if use_depth else None,
-                                               mask if use_depth else None, lambda_dssim, w_depth, loss_acc, buf)
+                                               mask if use_depth else None, lambda_dssim, w_depth, loss_acc, buf,
+                                               clamp=clamp, alpha_mask=alpha_mask)
     else:
         dcolor, ddepth, _ = rz.image_loss(color, target, invd if use_depth else None, prior if use_depth else None,
-                                          mask if use_depth else None, 1.0, w_depth, loss_acc)
-    launches += rz.LAUNCHES_LOSS
+                                          mask if use_depth else None, 1.0, w_depth, loss_acc, clamp=clamp,
+                                          alpha_mask=alpha_mask)
+    launches += rz.LAUNCHES.loss
     rz.rasterize_gaussians_backward(
         rs.bg, gaussians["means3D"], radii, empty if colors is None else colors, gaussians["opacities"],
         gaussians["scales"], gaussians["rotations"], rs.scale_modifier, empty, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
         rs.tanfovy, dcolor, ddepth, empty if shs is None else shs, rs.sh_degree, rs.campos, geom, num_rendered, binning,
         img, rs.antialiasing, rs.debug, accumulate_into=acc, dc=dc, raw_params=raw)
-    launches += rz.LAUNCHES_BACKWARD
+    launches += rz.LAUNCHES.backward
     return dict(num_rendered=num_rendered, launches=launches, radii=radii, color=color, invdepth=invd)
 
 
@@ -166,8 +170,9 @@ class ViewParallelRasterizer:
         self._copy_stream = None
         self._color_grads = None
 
-    def _upload(self, i, targets, priors, masks):
-        items = [targets[i], None if priors is None else priors.get(i), None if masks is None else masks.get(i)]
+    def _upload(self, i, targets, priors, masks, alphas=None):
+        items = [targets[i], None if priors is None else priors.get(i), None if masks is None else masks.get(i),
+                 None if alphas is None else alphas.get(i)]
         if self.device.type != "cuda" or all(t is None or t.device == self.device for t in items):
             return items, None
         if self._copy_stream is None:
@@ -259,13 +264,17 @@ class ViewParallelRasterizer:
     def step(self, gaussians: Dict[str, torch.Tensor], views: Sequence, targets: Dict[int, torch.Tensor],
              priors: Optional[Dict[int, torch.Tensor]] = None, masks: Optional[Dict[int, torch.Tensor]] = None,
              w_depth: float = 0.0, reduce: bool = True, keep_outputs: bool = False, lambda_dssim: float = 0.0,
-             prefetch_gaussians: Optional[Dict[str, torch.Tensor]] = None) -> Dict:
+             prefetch_gaussians: Optional[Dict[str, torch.Tensor]] = None, clamp: bool = True,
+             alpha_masks: Optional[Dict[int, torch.Tensor]] = None) -> Dict:
         """gaussians: means3D/shs/opacities/scales/rotations (post-activation, as render() passes them,
         /root/reference/gaussian_renderer/__init__.py:57-112); optionally `shs_dc` + `shs_rest` instead of `shs`
         (features_dc / features_rest, gradients then in buf.view("shs_dc") / ("shs_rest")) and `raw_params=True`
         (opacities / scales / rotations are the pre-activation parameters, gradients w.r.t. them); views: one GaussianRasterizationSettings per
         camera of the WHOLE batch (identical on every rank); targets/priors/masks: dict view index -> tensor
         for at least this rank's shard.  Returns summed-over-views gradients (all ranks) in self.buf.
+        clamp (default True) / alpha_masks (view index -> [1,H,W]): the loss of every view is taken on
+        clamp(render, 0, 1) * alpha_mask, what the reference's render() and training step do before l1_loss / ssim
+        (gaussian_renderer/__init__.py:121, train.py:148-150).
 
         prefetch_gaussians: pinned HOST tensors of the NEXT step's Gaussians.  They are uploaded during this step, one
         slice per view, on the same copy stream and behind that view's image upload (host->device copies of different
@@ -306,18 +315,19 @@ class ViewParallelRasterizer:
             """The views `sub` = [(k, i), ...] of one lane, in order, on the calling thread's current stream."""
             res = []
             scratch = self._scratch.setdefault(lane, {})
-            pending = self._upload(sub[0][1], targets, priors, masks) if sub else None
+            pending = self._upload(sub[0][1], targets, priors, masks, alpha_masks) if sub else None
             for n, (k, i) in enumerate(sub):
                 cur = pending
-                pending = self._upload(sub[n + 1][1], targets, priors, masks) if n + 1 < len(sub) else None
+                pending = self._upload(sub[n + 1][1], targets, priors, masks, alpha_masks) if n + 1 < len(sub) else None
                 if nxt is not None:
                     self._prefetch_slice(nxt, k, len(jobs))
-                tgt, pri, msk = self._await(cur)
+                tgt, pri, msk, alp = self._await(cur)
                 acc_k = dict(acc)  # per view: the slot that receives this view's masked colour gradient
                 if defer:
                     acc_k["color_grad_view"] = self._color_grads[k]
                 if self.backend is _cuda_view_backend:
-                    r = self.backend(gaussians, views[i], tgt, pri, msk, w_depth, acc_k, self.loss_acc, lambda_dssim, scratch)
+                    r = self.backend(gaussians, views[i], tgt, pri, msk, w_depth, acc_k, self.loss_acc, lambda_dssim, scratch,
+                                     clamp, alp)
                 else:
                     r = self.backend(gaussians, views[i], tgt, pri, msk, w_depth, acc_k, self.loss_acc)
                 res.append((k, r))
@@ -370,7 +380,7 @@ class ViewParallelRasterizer:
             else:
                 rz.sh_backward_views(gaussians["means3D"], gaussians["shs"], views[my[0]].sh_degree, campos,
                                      self._color_grads, acc["shs"], acc["means3D"], accumulate=False)
-            self.last_launches += rz.LAUNCHES_SH_BWD
+            self.last_launches += rz.LAUNCHES.sh_bwd
         if reduce and self.world > 1:
             self.buf.all_reduce(self.group)
             dist.all_reduce(self.loss_acc, op=dist.ReduceOp.SUM, group=self.group)

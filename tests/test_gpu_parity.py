@@ -197,6 +197,61 @@ def test_edge_cases():
                                rotations=z(4, 4))
 
 
+def test_non_finite_covariance_is_culled():
+    """NaN / inf scales or rotations (or exp() overflow of a raw scale) must cull the Gaussian, as upstream's
+    (int)NaN == 0 radius does, instead of reaching the binning with an inverted tile rect."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    sc = scenes.camera_relative_scene("nan", 17, 3000, 160, 96, 3.0, behind_frac=0.0)
+    view = sc.views[0]
+    bad = torch.arange(0, 3000, 7)
+    sc.scales[bad[0::4], 1] = float("nan")
+    sc.scales[bad[1::4], 0] = float("inf")
+    sc.rotations[bad[2::4], 2] = float("nan")
+    sc.means3D[bad[3::4], 0] = float("nan")
+    st = helpers.bit_structure(sc, view)
+    assert int(st["radii"][bad.numpy()].max()) == 0
+    lv, color, radii, invd = helpers.run_cuda(sc, view, DEV)
+    np.testing.assert_array_equal(radii.cpu().numpy(), st["radii"])
+    assert int(radii[bad.to(DEV)].max()) == 0 and int((radii > 0).sum()) > 2000
+    assert torch.isfinite(color).all() and torch.isfinite(invd).all()
+    sv, fn = _view_state(lv, radii, color, view)
+    assert fn.num_rendered == st["num_rendered"]
+    T = ((view.image_width + 15) // 16) * ((view.image_height + 15) // 16)
+    assert int(sv["sorted_tiles"].max()) < T
+    # identical to the scene without the bad Gaussians
+    keep = torch.ones(sc.P, dtype=torch.bool)
+    keep[bad] = False
+    sub = scenes.Scene("sub", sc.means3D[keep].contiguous(), sc.scales[keep].contiguous(), sc.rotations[keep].contiguous(),
+                       sc.opacities[keep].contiguous(), sc.shs[keep].contiguous(), sc.bg, sc.views)
+    with torch.no_grad():
+        _, c2, r2, d2 = helpers.run_cuda(sub, view, DEV)
+    assert torch.equal(color.detach(), c2) and torch.equal(invd.detach(), d2)
+    (color.sum() + invd.sum()).backward()
+    for k in ("means3D", "shs", "opacities", "scales", "rotations"):
+        assert float(lv[k].grad[bad.to(DEV)].abs().max()) == 0.0, k
+    # raw-parameter mode: exp() of a huge raw scale overflows to inf inside the kernel
+    rs = helpers.cuda_settings(sc, view, DEV)
+    raw_scales = torch.log(sub.scales).to(DEV)
+    raw_scales[::5, 0] = 200.0
+    with torch.no_grad():
+        c3, r3, d3 = GaussianRasterizer(rs)(means3D=sub.means3D.to(DEV), means2D=torch.zeros(sub.P, 3, device=DEV),
+                                            opacities=torch.logit(sub.opacities.clamp(1e-6, 1 - 1e-6)).to(DEV),
+                                            shs=sub.shs.to(DEV), scales=raw_scales, rotations=sub.rotations.to(DEV),
+                                            raw_params=True)
+    assert int(r3[::5].max()) == 0 and torch.isfinite(c3).all() and torch.isfinite(d3).all()
+
+
+def test_prefiltered_is_rejected():
+    """prefiltered=True traps upstream when a point is culled; the reference always passes False
+    (/root/reference/gaussian_renderer/__init__.py:47).  Here it raises instead of being silently ignored."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    sc = scenes.camera_relative_scene("pf", 5, 100, 64, 64, 3.0)
+    rs = helpers.cuda_settings(sc, sc.views[0], DEV)._replace(prefiltered=True)
+    lv = helpers.cuda_leaves(sc, DEV)
+    with pytest.raises(Exception, match="prefiltered"):
+        GaussianRasterizer(rs)(**lv)
+
+
 def test_forward_only_and_none_cotangents():
     sc = scenes.camera_relative_scene("n", 13, 3000, 128, 96, 3.0)
     view = sc.views[0]

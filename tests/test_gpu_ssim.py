@@ -124,3 +124,42 @@ def test_full_size_properties():
     _, _, acc_ab = rz.image_loss_ssim(a, b, lambda_dssim=0.2)
     _, _, acc_ba = rz.image_loss_ssim(b, a, lambda_dssim=0.2)
     assert abs(float(acc_ab[2]) - float(acc_ba[2])) <= 1e-6 and abs(float(acc_ab[0]) - float(acc_ba[0])) <= 1e-6
+
+
+@pytest.mark.parametrize("shape,use_alpha", [((3, 45, 70), True), ((3, 64, 96), True), ((3, 33, 31), False)])
+def test_training_loss_clamps_like_render_and_masks_like_train(shape, use_alpha):
+    """The RAW rasterizer colour may leave [0, 1]; the reference clamps it in render()
+    (/root/reference/gaussian_renderer/__init__.py:121) and multiplies by the camera's alpha mask (train.py:148-150)
+    before l1_loss / ssim.  pdgs_image_loss_ssim and pdgs_image_loss do both inside the kernels: values, and the
+    cotangent w.r.t. the raw colour (zero outside [0, 1]), against autograd of clamp -> mask -> loss in float64."""
+    from pdgs_b200 import rasterizer as rz
+    _, H, W = shape
+    gen = torch.Generator().manual_seed(H * 13 + W)
+    raw = torch.rand(*shape, generator=gen) * 1.7 - 0.3           # ~18 % below 0, ~24 % above 1
+    raw[0, 0, 0], raw[1, 0, 0] = 0.0, 1.0                        # the closed ends pass the gradient (torch.clamp)
+    tgt = torch.rand(*shape, generator=gen)
+    alpha = (torch.rand(1, H, W, generator=gen) > 0.25).float() * torch.rand(1, H, W, generator=gen) if use_alpha else None
+    lam = 0.2
+    x = raw.double().requires_grad_(True)
+    img = x.clamp(0, 1)
+    if alpha is not None:
+        img = img * alpha.double()
+    loss, parts = so.training_loss(img, tgt.double(), lam)
+    (g,) = torch.autograd.grad(loss, x)
+    dcolor, _, acc = rz.image_loss_ssim(raw.to(DEV), tgt.to(DEV), lambda_dssim=lam, clamp=True,
+                                        alpha_mask=None if alpha is None else alpha.to(DEV))
+    assert abs(float(acc[0]) - float(parts["l1"])) <= MEAN_TOL and abs(float(acc[2]) - float(parts["ssim"])) <= MEAN_TOL
+    assert float((dcolor.double().cpu() - g).abs().max()) <= GRAD_REL * float(g.abs().max())
+    outside = (raw < 0) | (raw > 1)
+    assert float(dcolor.cpu()[outside].abs().max()) == 0.0 and bool(outside.any())
+    # without the clamp the same call differentiates the raw image (the fused_ssim / l1_loss semantics)
+    d_raw, _, _ = rz.image_loss_ssim(raw.to(DEV), tgt.to(DEV), lambda_dssim=lam, clamp=False)
+    assert float(d_raw.cpu()[outside].abs().max()) > 0.0
+    # plain L1 entry point
+    x2 = raw.double().requires_grad_(True)
+    img2 = x2.clamp(0, 1) * (alpha.double() if alpha is not None else 1.0)
+    l1 = (img2 - tgt.double()).abs().mean()
+    (g2,) = torch.autograd.grad(l1, x2)
+    d1, _, acc1 = rz.image_loss(raw.to(DEV), tgt.to(DEV), clamp=True, alpha_mask=None if alpha is None else alpha.to(DEV))
+    assert abs(float(acc1[0]) - float(l1)) <= MEAN_TOL
+    assert float((d1.double().cpu() - g2).abs().max()) <= 1e-6 * float(g2.abs().max())

@@ -50,9 +50,10 @@ def test_batch_step_equals_sum_of_single_view_autograd():
         torch.zeros(sc.P, dtype=torch.int32, device=DEV), 0.0
     for i, view in enumerate(sc.views):
         lv, color, radii, invd = helpers.run_cuda(sc, view, DEV)
-        l = (color - targets[i]).abs().mean() + w_depth * ((invd - priors[i]) * masks[i]).abs().mean()
+        image = color.clamp(0, 1)  # what render() returns (/root/reference/gaussian_renderer/__init__.py:121)
+        l = (image - targets[i]).abs().mean() + w_depth * ((invd - priors[i]) * masks[i]).abs().mean()
         l.backward()
-        loss += float((color - targets[i]).abs().mean())
+        loss += float((image - targets[i]).abs().mean())
         g = {k: lv[k].grad for k in ("means3D", "shs", "opacities", "scales", "rotations")}
         sums = g if sums is None else {k: sums[k] + g[k] for k in g}
         vis = radii > 0
@@ -99,12 +100,17 @@ def test_batch_step_with_ssim_training_loss_equals_autograd_through_the_dropin_p
     gen = torch.Generator().manual_seed(5)
     targets = {i: torch.rand(3, H, W, generator=gen).to(DEV) for i in range(3)}
     priors = {i: torch.rand(1, H, W, generator=gen).to(DEV) for i in range(3)}
+    alphas = {i: (torch.rand(1, H, W, generator=gen) > 0.2).float().to(DEV) for i in range(3)}
     lam, w_depth = 0.2, 0.5
     sums, ssim_sum = None, 0.0
+    over = 0
     for i, view in enumerate(sc.views):
         lv, color, radii, invd = helpers.run_cuda(sc, view, DEV)
-        s = fused_ssim(color.unsqueeze(0), targets[i].unsqueeze(0))
-        l = (1.0 - lam) * (color - targets[i]).abs().mean() + lam * (1.0 - s) + w_depth * (invd - priors[i]).abs().mean()
+        over += int((color > 1).sum())
+        image = color.clamp(0, 1)    # /root/reference/gaussian_renderer/__init__.py:121
+        image = image * alphas[i]    # /root/reference/train.py:148-150
+        s = fused_ssim(image.unsqueeze(0), targets[i].unsqueeze(0))
+        l = (1.0 - lam) * (image - targets[i]).abs().mean() + lam * (1.0 - s) + w_depth * (invd - priors[i]).abs().mean()
         l.backward()
         ssim_sum += float(s)
         g = {k: lv[k].grad for k in ("means3D", "shs", "opacities", "scales", "rotations")}
@@ -112,7 +118,8 @@ def test_batch_step_with_ssim_training_loss_equals_autograd_through_the_dropin_p
     vp = ViewParallelRasterizer(sc.P, 16, DEV)
     gaussians = {k: getattr(sc, k).to(DEV) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
     views = [helpers.cuda_settings(sc, v, DEV) for v in sc.views]
-    vp.step(gaussians, views, targets, priors, None, w_depth, lambda_dssim=lam)
+    assert over > 0, "the scene must saturate some pixels, or the clamp is not exercised"
+    vp.step(gaussians, views, targets, priors, None, w_depth, lambda_dssim=lam, alpha_masks=alphas)
     for k in sums:
         assert helpers.rel_err(vp.buf.view(k), sums[k].view_as(vp.buf.view(k))) < 1e-4, k
     assert abs(float(vp.loss_acc[2]) - ssim_sum) < 1e-4
