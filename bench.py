@@ -50,7 +50,10 @@ def parse_args():
     ap.add_argument("--scale-image", type=float, default=1.0, help="debugging only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--cpu-window", type=int, nargs=2, default=[12, 8], help="tile window of the CPU sample")
+    ap.add_argument("--cpu-window", type=int, nargs=2, default=[8, 6], help="tile window of the CPU sample")
+    ap.add_argument("--no-dropin", action="store_true", help="skip the drop-in API row")
+    ap.add_argument("--no-library-baselines", action="store_true", help="skip the CUB / reference fused-ssim rows")
+    ap.add_argument("--dropin-only", action="store_true", help=argparse.SUPPRESS)  # child process of the dropin row
     return ap.parse_args()
 
 
@@ -63,64 +66,63 @@ def measured_peaks():
 
 
 # --------------------------------------------------------------------------------------------
-# CPU arm: the float64 oracle on a bounded sample (tile window of one view), extrapolated by pairs
+# CPU arm: the float64 oracle on bounded samples (tile windows of one view), extrapolated by pairs
 # --------------------------------------------------------------------------------------------
-def oracle_sample(scene, view, window_tiles, threads, return_oracle=False):
-    """fwd+bwd of the oracle on the Gaussians touching a centred window of tiles of `view`.
-    Returns (seconds, pairs in the window, pairs in the whole view)."""
-    import numpy as np
-    from oracle import bitmodel
-    from oracle.raster_oracle import Oracle, Settings
+CPU_POSITIONS = ((0.5, 0.5), (0.25, 0.3), (0.75, 0.7), (0.3, 0.75), (0.7, 0.25))
+
+
+def oracle_sample(scene, view, window_tiles, threads, return_oracle=False, position=(0.5, 0.5), st=None):
+    """fwd+bwd of the oracle (oracle/window.py) on the Gaussians touching a window of tiles of `view`.
+    Returns (seconds, pairs in the window, pairs in the whole view, Gaussians in the window)."""
+    from oracle import window as ow
     torch.set_num_threads(threads)
     W, H = view.image_width, view.image_height
-    gx, gy = (W + 15) // 16, (H + 15) // 16
-    tw, th = min(window_tiles[0], gx), min(window_tiles[1], gy)
-    x0, y0 = (gx - tw) // 2, (gy - th) // 2
-    win = (x0, y0, x0 + tw, y0 + th)
-    st = bitmodel.preprocess(scene.means3D, scene.scales, 1.0, scene.rotations, None, view.world_view_transform,
-                             view.full_proj_transform, W, H, np.float32(view.tanfovx), np.float32(view.tanfovy))
-    rect, vis = st["rect"], st["radii"] > 0
-    hit = vis & (rect[:, 0] < win[2]) & (rect[:, 2] > win[0]) & (rect[:, 1] < win[3]) & (rect[:, 3] > win[1])
-    ids = torch.from_numpy(np.nonzero(hit)[0])
-    cx0, cx1 = np.clip(rect[hit, 0], win[0], win[2]), np.clip(rect[hit, 2], win[0], win[2])
-    cy0, cy1 = np.clip(rect[hit, 1], win[1], win[3]), np.clip(rect[hit, 3], win[1], win[3])
-    pairs_window = int(((cx1 - cx0) * (cy1 - cy0)).sum())
-    pairs_view = int(st["num_rendered"])
-    sub = {k: (v[hit] if hasattr(v, "shape") and v.shape[:1] == hit.shape else v) for k, v in st.items()}
-    sub["num_rendered"] = int(sub["tiles"].sum())
-    s = Settings(image_height=H, image_width=W, tanfovx=view.tanfovx, tanfovy=view.tanfovy, bg=scene.bg,
-                 scale_modifier=1.0, viewmatrix=view.world_view_transform, projmatrix=view.full_proj_transform,
-                 sh_degree=scene.sh_degree, campos=view.camera_center)
+    win = ow.place_window(W, H, window_tiles, position)
+    if st is None:
+        st = ow.structure(scene, view)
     gen = torch.Generator().manual_seed(7)
     target = torch.rand(3, H, W, generator=gen, dtype=torch.float64)
     t0 = time.perf_counter()
-    o = Oracle(s, scene.means3D[ids], scene.opacities[ids], shs=scene.shs[ids], scales=scene.scales[ids],
-               rotations=scene.rotations[ids], need_grad=True, structure=sub, tile_window=win)
+    o, ids, info = ow.window_oracle(scene, view, win, st=st, need_grad=True)
     res = o.forward()
-    gc = torch.sign(res.color - target) / target.numel()
+    img = res.color.clamp(0, 1)
+    gc = torch.sign(img - target) / target.numel() * ((res.color >= 0) & (res.color <= 1))
     o.backward(gc, None)
     dt = time.perf_counter() - t0
     if return_oracle:
-        return dt, pairs_window, pairs_view, int(ids.numel()), dict(result=res, window=win, ids=ids)
-    return dt, pairs_window, pairs_view, int(ids.numel())
+        return dt, info["pairs_window"], info["pairs_view"], int(ids.numel()), dict(result=res, window=win, ids=ids)
+    return dt, info["pairs_window"], info["pairs_view"], int(ids.numel())
 
 
-def cpu_arm(args, scene, steps, warmup):
+def cpu_arm(args, scene, positions, samples, warm):
+    """`positions` window positions of view 0, per position `warm` untimed + `samples` timed fwd+bwd passes of the oracle.
+    Every sample is extrapolated to a whole view by its own pair count; the value is the mean over all timed samples and
+    the spread over positions is reported (the figure is an EXTRAPOLATED sample, not a measured whole-view time)."""
+    from oracle import window as ow
     threads = os.cpu_count() or 1
     view = scene.views[0]
-    times, info = [], None
-    for it in range(warmup + steps):
-        dt, pw, pv, n = oracle_sample(scene, view, args.cpu_window, threads)
-        info = (pw, pv, n)
-        if it >= warmup:
-            times.append(dt)
-    pw, pv, n = info
-    t_sample = sum(times) / len(times)
-    t_view = t_sample * pv / max(pw, 1)
-    sample = (f"float64 PyTorch-CPU oracle, fwd+bwd, {args.cpu_window[0]}x{args.cpu_window[1]}-tile centred window of "
-              f"view 0 ({n} Gaussians, {pw} of {pv} (tile,Gaussian) pairs); {t_sample:.2f} s per sample, "
-              f"extrapolated to a whole view by pairs")
-    return dict(value=1.0 / t_view, unit=UNIT, cores=threads, kind="port", sample=sample), t_sample
+    st = ow.structure(scene, view)
+    per_pos, all_t, all_v, frac = [], [], [], []
+    for pos in CPU_POSITIONS[:positions]:
+        vals = []
+        for it in range(warm + samples):
+            dt, pw, pv, n = oracle_sample(scene, view, args.cpu_window, threads, position=pos, st=st)
+            if it >= warm:
+                vals.append(1.0 / (dt * pv / max(pw, 1)))
+                all_t.append(dt)
+        frac.append(pw / max(pv, 1))
+        per_pos.append(dict(position=list(pos), gaussians=n, pairs_window=pw, views_per_s=sum(vals) / len(vals),
+                            min=min(vals), max=max(vals)))
+        all_v.extend(vals)
+    value = sum(all_v) / len(all_v)
+    t_sample = sum(all_t) / len(all_t)
+    sample = (f"float64 PyTorch-CPU oracle (clamp + L1 loss), fwd+bwd, {args.cpu_window[0]}x{args.cpu_window[1]}-tile windows of "
+              f"view 0 at {len(per_pos)} position(s), {warm} warm + {samples} timed passes each; a pass covers "
+              f"{100 * sum(frac) / len(frac):.2f} % of the view's {pv} (tile,Gaussian) pairs and takes {t_sample:.2f} s; "
+              f"EXTRAPOLATED to a whole view by pair count")
+    return dict(value=value, unit=UNIT, cores=threads, kind="port", sample=sample, extrapolated=True,
+                sample_fraction=sum(frac) / len(frac), spread=dict(min=min(all_v), max=max(all_v)),
+                per_position=per_pos), t_sample
 
 
 # --------------------------------------------------------------------------------------------
@@ -221,6 +223,123 @@ def stop_clock_sampler(proc, path):
     return out
 
 
+def _pct(xs, q):
+    xs = sorted(xs)
+    return xs[min(len(xs) - 1, max(0, int(round(q * (len(xs) - 1)))))]
+
+
+def dropin_row(args, scene, dev, iters=50, warmup=10):
+    """SURVEY 8(d) timing protocol on the DROP-IN API: `GaussianRasterizer.forward` + `loss.backward()` of the caller's
+    loss `|clamp(render, 0, 1) - gt|.mean()` (torch ops, as /root/reference/gaussian_renderer/__init__.py:121 and
+    train.py:153 do), one view per iteration cycling through the cameras, CUDA events, 10 warm-up + 50 timed,
+    median / p10 / p90.  Honours CUDA_LAUNCH_BLOCKING from the environment (the reference sets it, train.py:65)."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    from pdgs_b200 import scenes
+    torch.cuda.set_device(dev)
+    lv = {k: getattr(scene, k).to(dev).requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    means2D = torch.zeros(scene.P, 3, device=dev, requires_grad=True)
+    n = min(len(scene.views), 8)
+    rast, tgts = [], []
+    for i in range(n):
+        v = scene.views[i]
+        rs = GaussianRasterizationSettings(
+            image_height=v.image_height, image_width=v.image_width, tanfovx=v.tanfovx, tanfovy=v.tanfovy, bg=scene.bg.to(dev),
+            scale_modifier=1.0, viewmatrix=v.world_view_transform.to(dev), projmatrix=v.full_proj_transform.to(dev),
+            sh_degree=scene.sh_degree, campos=v.camera_center.to(dev), prefiltered=False, debug=False, antialiasing=False)
+        rast.append(GaussianRasterizer(raster_settings=rs))
+        gen = torch.Generator().manual_seed(scenes.SEED0 + 1000 + i)
+        tgts.append(torch.rand(3, v.image_height, v.image_width, generator=gen).to(dev))
+    fwd, tot = [], []
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    for it in range(warmup + iters):
+        for t in list(lv.values()) + [means2D]:
+            t.grad = None
+        k = it % n
+        ev[0].record()
+        color, radii, invd = rast[k](means3D=lv["means3D"], means2D=means2D, opacities=lv["opacities"], shs=lv["shs"],
+                                     scales=lv["scales"], rotations=lv["rotations"])
+        ev[1].record()
+        loss = (color.clamp(0, 1) - tgts[k]).abs().mean()
+        loss.backward()
+        ev[2].record()
+        torch.cuda.synchronize(dev)
+        if it >= warmup:
+            fwd.append(ev[0].elapsed_time(ev[1]))
+            tot.append(ev[0].elapsed_time(ev[2]))
+    return dict(api="diff_gaussian_rasterization.GaussianRasterizer.forward + loss.backward() (torch clamp + L1 loss), one view "
+                    "per call", iters=iters, warmup=warmup, cuda_launch_blocking=os.environ.get("CUDA_LAUNCH_BLOCKING", "") == "1",
+                fwd_ms=dict(median=_pct(fwd, 0.5), p10=_pct(fwd, 0.1), p90=_pct(fwd, 0.9)),
+                fwd_bwd_ms=dict(median=_pct(tot, 0.5), p10=_pct(tot, 0.1), p90=_pct(tot, 0.9)),
+                views_per_s=1e3 / _pct(tot, 0.5))
+
+
+def dropin_row_blocking(args):
+    """The same row in a child process with CUDA_LAUNCH_BLOCKING=1 (it must be set before CUDA initialises)."""
+    env = dict(os.environ, CUDA_LAUNCH_BLOCKING="1")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    cmd = [sys.executable, os.path.abspath(__file__), "--dropin-only", "--config", args.config, "--views", str(min(args.views, 8)),
+           "--scale-image", str(args.scale_image)] + (["--P", str(args.P)] if args.P else [])
+    try:
+        r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+        for ln in reversed(r.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                return json.loads(ln)
+        return dict(error=(r.stderr or r.stdout)[-400:])
+    except Exception as e:  # noqa: BLE001
+        return dict(error=f"{type(e).__name__}: {e}")
+
+
+def library_baselines(scene, view_settings, g_dev, dev, H, W, P):
+    """GPU denominators on the same box (tools/gpu_baselines.py): the reference rasterizer's K2 / K4 library calls
+    (cub::DeviceScan::InclusiveSum, cub::DeviceRadixSort::SortPairs on the reference-format 64-bit keys) on the arrays
+    of one real view, and the reference's fused-ssim CUDA extension next to pdgs_image_loss_ssim."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gpu_baselines as gb
+    from pdgs_b200 import rasterizer as rz
+    out = {}
+    if gb.cub() is not None:
+        rs = view_settings
+        empty = torch.empty(0, device=dev)
+        with torch.no_grad():
+            R, color, radii, geom, binning, img, invd = rz.rasterize_gaussians(
+                rs.bg, g_dev["means3D"], empty, g_dev["opacities"], g_dev["scales"], g_dev["rotations"], 1.0, empty,
+                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, H, W, g_dev["shs"], rs.sh_degree, rs.campos, False,
+                False, False)
+        sv = rz.state_view(geom, binning, img, P, W, H, R, to_cpu=False)
+        ku, vu = gb.reference_binning_inputs(sv)
+        T = ((W + 15) // 16) * ((H + 15) // 16)
+        c = gb.cub_binning(sv["tiles_touched"], ku, vu, T, warmup=5, iters=30)
+        out["cub"] = dict(
+            what="reference K2 + K4 library calls on this view's arrays: cub::DeviceScan::InclusiveSum(tiles_touched[P]) and "
+                 "cub::DeviceRadixSort::SortPairs(u64 tile<<32|depth, u32 id) over bits [0, 32+bits(T)); CUDA 12.9 CUB",
+            P=P, R=int(R), end_bit=c["end_bit"], scan_ms=c["scan_ms"], sort_pairs_u64_ms=c["sort_ms"],
+            sorted_list_equals_ours=bool(torch.equal(c["sorted_vals"], sv["point_list"]) and
+                                         torch.equal(c["sorted_keys"], sv["sorted_keys"])))
+        del sv, ku, vu, c
+    else:
+        out["cub"] = dict(unavailable="tools/libcub_baseline.so not built")
+    try:
+        out["fused_ssim"] = gb.ssim_loss_baseline(H, W, dev)
+        if out["fused_ssim"].get("reference_ms") is None:
+            out["fused_ssim"]["unavailable"] = "oracle/_ref/fused_ssim_cuda.so not built"
+    except Exception as e:  # noqa: BLE001
+        out["fused_ssim"] = dict(error=f"{type(e).__name__}: {e}"[:300])
+    torch.cuda.empty_cache()
+    return out
+
+
+def grad_checksum(buf):
+    """Per-segment (sum g, sum |g|) of the all-reduced flat gradient buffer in float64, and the sum of max_radii2D: equal
+    (to fp32 reassociation) for every N if N GPUs compute what one GPU computes (SURVEY 8(e) semantics note)."""
+    out = {}
+    for name in ("means3D", "shs", "opacities", "scales", "rotations", "densify_grad_accum", "densify_denom"):
+        t = buf.view(name).double()
+        out[name] = [float(t.sum()), float(t.abs().sum())]
+    out["max_radii2D"] = int(buf.max_radii2D.sum(dtype=torch.int64))
+    return out
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -228,20 +347,31 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     from pdgs_b200 import scenes
 
+    if args.dropin_only:
+        print(json.dumps(dropin_row(args, scenes.make_config(args.config, P=args.P, n_views=args.views,
+                                                             scale_image=args.scale_image), torch.device("cuda", 0))))
+        return 0
+
     if args.impl == "reference":
         if rank != 0:
             return 0
         scene = scenes.make_config(args.config, P=args.P, n_views=args.views, scale_image=args.scale_image)
         t0 = time.perf_counter()
-        base, t_sample = cpu_arm(args, scene, max(1, args.steps), max(0, min(args.warmup, 1)))
+        # K timed steps = K bounded samples of the workload (fwd+bwd of a tile window of a view), spread over three window
+        # positions, at most 12 in total so the arm ends within a few minutes; one warm pass per position
+        per_pos = max(1, min(4, -(-max(1, args.steps) // 3)))
+        base, t_sample = cpu_arm(args, scene, 3, per_pos, 1 if args.warmup > 0 else 0)
         line = dict(impl="reference", metric=METRIC, value=base["value"], unit=UNIT, n_gpus=args.gpus, steps=args.steps,
-                    warmup=args.warmup, ms_per_step=1e3 * args.views / base["value"], higher_is_better=True,
-                    scaling="strong", vs_baseline=None, dtype="f64", data="synthetic",
-                    config=workload_config(args, scene, world=1), cpu_baseline=base,
+                    warmup=args.warmup, ms_per_step=1e3 * t_sample, steps_timed=3 * per_pos, higher_is_better=True,
+                    scaling="strong", vs_baseline=None, dtype="f64", data="synthetic", extrapolated=True,
+                    config=workload_config(args, scene, world=max(1, args.gpus)), cpu_baseline=base,
                     e2e=dict(value=base["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                     gpu_launches=0, wall_s=time.perf_counter() - t0,
-                    note="the reference rasterizer is CUDA-only and its source is absent from the checkout; this arm is "
-                         "the float64 CPU transcription of its maths (oracle/) on the host cores")
+                    note="EXTRAPOLATED CPU-ORACLE SAMPLE, not a speed-up denominator: the reference rasterizer is CUDA-only and "
+                         "its source is absent from the checkout (empty submodule), so this arm times the float64 CPU "
+                         "transcription of its maths (oracle/) on tile windows of one view (`ms_per_step` = one measured "
+                         "sample) and scales by pair count to views/s.  GPU-side denominators (CUB, the reference's "
+                         "fused-ssim kernel) are in the b200 arm's `library_baselines`.")
         print(json.dumps(line))
         return 0
 
@@ -309,6 +439,8 @@ def main():
     barrier()
     clocks = stop_clock_sampler(sampler, sampler_path) if rank == 0 else None
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    checksum = grad_checksum(vp.buf)          # of the last timed step's all-reduced gradients (identical on all ranks)
+    loss_sums_resident = [float(v) for v in vp.loss_acc.cpu()]
     # Per-stage durations (roofline / stages): a second measured region of the same steps with ONE view in flight.  In
     # the region above `lanes` views run concurrently on separate streams, so a stage's event pair would also cover
     # kernels of other views; one view at a time gives each kernel's own duration (the figure ncu's launch list shows).
@@ -336,7 +468,7 @@ def main():
     ms_total = float(ms.item())
     n_views = len(scene.views)
     value = n_views * args.steps / (ms_total * 1e-3)
-    loss_mean = float(vp.loss_acc[0].item()) / n_views
+    loss_mean = loss_sums_resident[0] / n_views
 
     # ---------------- algorithmic work of this rank's views (untimed pass) ----------------
     work = dict(P=P, V=0, R=0, n_test=0, n_acc=0, n_test_bwd=0, views=len(my), tiles=((W + 15) // 16) * ((H + 15) // 16),
@@ -382,6 +514,20 @@ def main():
         for _ in range(max(1, min(args.warmup, 2))):
             e2e_step(prefetch_next=False)
         barrier()
+        # N > 1: every rank uploaded 1/world of each tensor and an in-place all-gather over NVLink completed the
+        # replicas; they must equal the host tensors bit for bit on every rank
+        replicas_ok = None
+        if world > 1:
+            staged_dev, ev = vp.stage_gaussians(host)
+            if ev is not None:
+                torch.cuda.current_stream(dev).wait_event(ev)
+            ok = all(torch.equal(staged_dev[k].cpu(), host[k]) for k in host)
+            flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            replicas_ok = bool(flag.item())
+            assert replicas_ok, "gathered parameter replicas differ from the host tensors"
+            del staged_dev
+            barrier()
         h2d0 = vp.h2d_bytes
         t0 = time.perf_counter()
         e0.record()
@@ -403,7 +549,8 @@ def main():
                    api="pdgs_b200.viewparallel.ViewParallelRasterizer.step (C ABI: pdgs_forward / pdgs_image_loss / "
                        "pdgs_backward) fed from pinned host tensors; step k+1's Gaussians are uploaded during step k (each rank its "
                        "1/world share over PCIe, replicas completed by an all-gather over NVLink), target images one view ahead",
-                   loss_mean=float(last[0].item()) / n_views)
+                   loss_mean=float(last[0].item()) / n_views, replicas_equal_host=replicas_ok,
+                   grad_checksum=grad_checksum(vp.buf))
 
     if rank != 0:
         if world > 1:
@@ -465,15 +612,44 @@ def main():
                         peak_source=("MEASURED_PEAKS.json hbm_gbs (%s)" % peaks["source"]) if top["bound"] == "hbm" else
                         "derived: 148 SMs x 128 fp32 lanes x 2 x sm_max_mhz (MEASURED_PEAKS.json has no fp32 SIMT figure)")
 
+    lib = None
+    if not args.no_library_baselines:
+        lib = library_baselines(scene, views_dev[my[0]], g_dev, dev, H, W, P)
+        cubr = lib.get("cub", {})
+        for st_ in stages:
+            if st_["stage"] in ("sort", "depth_sort") and "sort_pairs_u64_ms" in cubr:
+                st_["library_baseline_ms"] = cubr["sort_pairs_u64_ms"]["median"]
+                st_["library_baseline"] = ("cub::DeviceRadixSort::SortPairs over the reference's 64-bit keys: the ONE sort "
+                                           "the reference runs where this pipeline runs depth_sort + sort")
+            if st_["stage"] == "duplicate" and "scan_ms" in cubr:
+                st_["library_baseline_ms"] = cubr["scan_ms"]["median"]
+                st_["library_baseline"] = "cub::DeviceScan::InclusiveSum (the scan fused into this kernel)"
+        t = {s_["stage"]: s_["avg_ms"] for s_ in stages}
+        if "sort_pairs_u64_ms" in cubr:
+            cubr["ours_ms"] = dict(depth_sort=t.get("depth_sort"), scan_duplicate=t.get("duplicate"), tile_sort=t.get("sort"))
+            cubr["ours_sorts_ms"] = (t.get("depth_sort") or 0.0) + (t.get("sort") or 0.0)
+            cubr["reference_sort_plus_scan_ms"] = cubr["sort_pairs_u64_ms"]["median"] + cubr["scan_ms"]["median"]
+        fs = lib.get("fused_ssim", {})
+        if "loss" in t and fs.get("reference_ms"):
+            fs["note"] = ("pdgs_image_loss_ssim = value + cotangent of (1-l)*L1 + l*(1-SSIM) on the raw render (clamp inside), "
+                          "3 launches; reference = the same through torch ops + the reference's fused-ssim extension")
+
+    dropin = None
+    if world == 1 and not args.no_dropin:
+        del vp
+        torch.cuda.empty_cache()
+        dropin = dict(default=dropin_row(args, scene, dev), launch_blocking=dropin_row_blocking(args))
+
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
-        cpu_baseline, _ = cpu_arm(args, scene, 1, 0)
+        cpu_baseline, _ = cpu_arm(args, scene, 1, 2, 1)
 
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
                 ms_per_step=ms_total / args.steps, ms_per_view_per_gpu=ms_total / args.steps / max(len(my), 1),
                 higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
                 config=workload_config(args, scene, world), clocks=clocks, e2e=e2e, gpu_launches=launches,
-                roofline=roofline, stages=stages, cpu_baseline=cpu_baseline,
+                roofline=roofline, stages=stages, cpu_baseline=cpu_baseline, library_baselines=lib, dropin=dropin,
+                grad_checksum=checksum, loss_sums=loss_sums_resident,
                 stage_timing=dict(lanes=1, ms_per_step=ms_one_lane,
                                   note="stages / roofline come from a second measured region of the same steps with one view "
                                        "in flight; `value` is measured with config.lanes views in flight on separate streams"),
@@ -489,7 +665,7 @@ def main():
 def workload_config(args, scene, world):
     v = scene.views[0]
     return dict(workload=f"{args.config}: {scene.P} Gaussians SH3, {len(scene.views)} cameras {v.image_width}x{v.image_height}, "
-                         f"fwd + L1 loss + bwd per view, grads summed over views",
+                         f"fwd + L1 loss on clamp(render,0,1) + bwd per view, grads summed over views",
                 gaussians=scene.P, views_per_step=len(scene.views), image=[v.image_width, v.image_height],
                 parallelism=f"view-parallel x{world} (Gaussians replicated, one all-reduce of [P,61] fp32 per step)",
                 lanes=int(os.environ.get("PDGS_LANES", "3")),

@@ -494,8 +494,8 @@ def sort_pairs(keys: torch.Tensor, vals: torch.Tensor, end_bit: int):
     return keys_out, vals_out
 
 
-def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int) -> dict:
-    """Copies of the saved state as torch tensors (parity tests)."""
+def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int, to_cpu: bool = True) -> dict:
+    """Copies of the saved state as torch tensors (parity tests); to_cpu=False keeps the copies on the device."""
     lib = L.lib()
     st = _state(geom, image, binning if binning.numel() else None, _binning_capacity(binning))
     v = L.PdgsStateView()
@@ -511,7 +511,8 @@ def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int) 
         for blob in (geom, binning, image):
             if blob.numel() and blob.data_ptr() <= ptr < blob.data_ptr() + blob.numel():
                 off = ptr - blob.data_ptr()
-                return blob[off:off + nbytes].view(dtype).clone().cpu()
+                t = blob[off:off + nbytes].view(dtype).clone()
+                return t.cpu() if to_cpu else t
         raise L.PdgsError("state view pointer outside the state blobs")
 
     R = int(num_rendered)

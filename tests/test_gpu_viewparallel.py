@@ -175,3 +175,62 @@ def test_lanes_match_one_view_at_a_time(split_raw):
         assert helpers.rel_err(b.buf.flat, a.buf.flat) < 1e-4
         assert torch.equal(b.buf.max_radii2D, a.buf.max_radii2D)
         assert torch.allclose(b.loss_acc, a.loss_acc, rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize("split", [False, True])
+def test_deferred_sh_backward_and_accumulating_k9_against_oracle(split):
+    """Direct oracle comparison of the batch path's two special kernels (no CUDA-vs-CUDA step in between): K9 in
+    accumulate mode (adds every view's gradients into the same buffers, leaves only the clamp-masked dL/drgb per view)
+    and pdgs_sh_backward_views(_split) (SH gradient + view-direction term of all views in one pass), against the SUM
+    over views of the float64 oracle's autograd gradients for random cotangents."""
+    from pdgs_b200 import rasterizer as rz
+    from pdgs_b200.viewparallel import GradBuffer
+    n_views = 4
+    sc = scenes.make_config("C4", P=6000, n_views=n_views, scale_image=0.12)
+    H, W = sc.views[0].image_height, sc.views[0].image_width
+    g = {k: getattr(sc, k).to(DEV) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    dc, rest = g["shs"][:, :1].contiguous(), g["shs"][:, 1:].contiguous()
+    buf = GradBuffer(sc.P, 16, DEV)
+    acc = buf.accumulate_dict(split)
+    color_grads = torch.empty(n_views, sc.P, 3, device=DEV)
+    empty = torch.empty(0, device=DEV)
+    want = None
+    accum_ref, denom_ref = torch.zeros(sc.P, dtype=torch.float64), torch.zeros(sc.P)
+    for i, view in enumerate(sc.views):
+        o, res, st = helpers.run_oracle(sc, view)
+        gen = torch.Generator().manual_seed(40 + i)
+        gc = torch.randn(3, H, W, generator=gen) / (3 * H * W)
+        gd = torch.randn(1, H, W, generator=gen) / (H * W)
+        ref = o.backward(gc, gd)
+        want = ref if want is None else {k: (want[k] + ref[k] if ref[k] is not None else None) for k in ref}
+        vis = torch.from_numpy(st["radii"] > 0)
+        accum_ref += ref["means2D"][:, :2].norm(dim=-1) * vis
+        denom_ref += vis.float()
+        rs = helpers.cuda_settings(sc, view, DEV)
+        R, color, radii, geom, binning, img, invd = rz.rasterize_gaussians(
+            rs.bg, g["means3D"], empty, g["opacities"], g["scales"], g["rotations"], 1.0, empty, rs.viewmatrix, rs.projmatrix,
+            rs.tanfovx, rs.tanfovy, H, W, rest if split else g["shs"], 3, rs.campos, False, False, False,
+            dc=dc if split else None)
+        np_radii = radii.cpu().numpy()
+        assert (np_radii == st["radii"]).all()
+        a = dict(acc)
+        a["color_grad_view"] = color_grads[i]
+        rz.rasterize_gaussians_backward(
+            rs.bg, g["means3D"], radii, empty, g["opacities"], g["scales"], g["rotations"], 1.0, empty, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, gc.to(DEV), gd.to(DEV), rest if split else g["shs"], 3, rs.campos, geom, R,
+            binning, img, False, False, accumulate_into=a, dc=dc if split else None)
+    campos = torch.stack([v.camera_center for v in sc.views]).to(DEV)
+    if split:
+        rz.sh_backward_views_split(g["means3D"], dc, rest, 3, campos, color_grads, acc["shs_dc"], acc["shs_rest"],
+                                   acc["means3D"], accumulate=False)
+    else:
+        rz.sh_backward_views(g["means3D"], g["shs"], 3, campos, color_grads, acc["shs"], acc["means3D"], accumulate=False)
+    torch.cuda.synchronize()
+    got_shs = torch.cat([buf.view("shs_dc"), buf.view("shs_rest")], dim=1) if split else buf.view("shs")
+    for k, got in (("means3D", buf.view("means3D")), ("shs", got_shs), ("opacities", buf.view("opacities")),
+                   ("scales", buf.view("scales")), ("rotations", buf.view("rotations"))):
+        e = helpers.rel_err(got, want[k].reshape(got.shape))
+        assert e <= 1e-3, (k, e)
+        assert helpers.elem_err(got, want[k].reshape(got.shape), floor_frac=2e-3) <= 0.05, k
+    assert helpers.rel_err(buf.view("densify_grad_accum"), accum_ref) <= 1e-3
+    assert torch.equal(buf.view("densify_denom").cpu(), denom_ref)
