@@ -519,8 +519,10 @@ def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int, 
     point_list = grab(v.point_list, R, torch.int32)
     sorted_tiles = grab(v.sorted_tiles, R, torch.int32)
     conic_opacity = grab(v.conic_opacity, P * 4, torch.float32).view(-1, 4)
+    rgb = grab(v.rgb, P * 4, torch.float32).view(-1, 4)
     # the reference's 64-bit sort key of every pair: (tile << 32) | depth bits of its Gaussian
-    depth_bits = conic_opacity[:, 3].contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+    depth32 = rgb[:, 2].contiguous().view(torch.int32)
+    depth_bits = depth32.to(torch.int64) & 0xFFFFFFFF
     sorted_keys = (sorted_tiles.to(torch.int64) << 32) | depth_bits[point_list.to(torch.int64)]
     return dict(
         point_list=point_list, sorted_keys=sorted_keys, sorted_tiles=sorted_tiles,
@@ -528,8 +530,7 @@ def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int, 
         n_contrib=grab(v.n_contrib, W * H, torch.int32), n_tested=grab(v.n_tested, W * H, torch.int32),
         n_accepted=grab(v.n_accepted, W * H, torch.int32), tiles_touched=grab(v.tiles_touched, P, torch.int32),
         point_offsets=grab(v.point_offsets, P, torch.int32), depth_order=grab(v.depth_order, P, torch.int32),
-        xy=grab(v.xy, P * 4, torch.float32).view(-1, 4), conic_opacity=conic_opacity,
-        rgb=grab(v.rgb, P * 4, torch.float32).view(-1, 4))
+        xy=grab(v.xy, P * 4, torch.float32).view(-1, 4), conic_opacity=conic_opacity, rgb=rgb, depth_bits=depth32)
 
 
 def image_counters(geom, binning, image, P: int, W: int, H: int) -> dict:

@@ -57,7 +57,7 @@ def _check_integers(sc, view, st, R, radii, state, with_bitmodel_sort):
     assert torch.equal(sv["tiles_touched"][vis].cpu(), torch.from_numpy(st["tiles"].view(np.int32))[vis.cpu()])
     assert torch.equal(sv["xy"][vis][:, :2].contiguous().view(torch.int32).cpu(),
                        torch.from_numpy(st["xy"].view(np.int32))[vis.cpu()])
-    assert torch.equal(sv["conic_opacity"][vis][:, 3].contiguous().view(torch.int32).cpu(),
+    assert torch.equal(sv["depth_bits"][vis].cpu(),
                        torch.from_numpy(st["depth_bits"].view(np.int32))[vis.cpu()])
     # the reference's K2 + K4 as library calls on the reference-format arrays
     ku, vu = gb.reference_binning_inputs(sv)

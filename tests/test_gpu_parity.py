@@ -38,7 +38,7 @@ def _check_ints(sc, view, lv, color, radii, st, scale_modifier=1.0, cov3d=None):
     assert fn.num_rendered == st["num_rendered"]
     np.testing.assert_array_equal(sv["tiles_touched"].numpy().view(np.uint32)[vis], st["tiles"][vis])
     np.testing.assert_array_equal(sv["xy"].numpy()[vis, :2].view(np.uint32), st["xy"][vis].view(np.uint32))
-    np.testing.assert_array_equal(sv["conic_opacity"].numpy()[vis, 3].view(np.uint32), st["depth_bits"][vis])
+    np.testing.assert_array_equal(sv["depth_bits"].numpy()[vis].view(np.uint32), st["depth_bits"][vis])
     np.testing.assert_array_equal(sv["point_list"].numpy().view(np.uint32), b["point_list"])
     np.testing.assert_array_equal(sv["sorted_keys"].numpy().view(np.uint64), b["keys"])
     np.testing.assert_array_equal(sv["ranges"].numpy().view(np.uint32), b["ranges"])
