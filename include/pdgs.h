@@ -260,7 +260,7 @@ int pdgs_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, ui
 typedef struct PdgsStateView {
   const uint32_t* point_list;   /* [R] sorted Gaussian ids */
   const uint32_t* sorted_tiles; /* [R] tile id of each sorted pair; the reference's 64-bit key of pair i is
-                                 *     (sorted_tiles[i] << 32) | bits(rgb[point_list[i]][2]) */
+                                 *     (sorted_tiles[i] << 32) | bits(conic_opacity[point_list[i]][3]) */
   const uint32_t* ranges;       /* [T,2] */
   const float* final_T;         /* [H*W] */
   const uint32_t* n_contrib;    /* [H*W] */
@@ -269,11 +269,9 @@ typedef struct PdgsStateView {
   const uint32_t* tiles_touched;/* [P] */
   const uint32_t* point_offsets;/* [P] inclusive scan of tiles_touched taken in depth order */
   const uint32_t* depth_order;  /* [P] Gaussian indices sorted by (depth bits, index); culled ones last */
-  /* per-Gaussian records in the blend-ready form the kernels gather (log2e = 1.442695...): */
-  const float* xy;              /* [P,4] (x, y, -0.5*log2e*conic.x, -log2e*conic.y) */
-  const float* conic_opacity;   /* [P,4] (-0.5*log2e*conic.z, log2(opacity*h), 1/depth, r) */
-  const float* rgb;             /* [P,4] (g, b, depth, clamped-bits); depth = view-space z, whose bit pattern is the
-                                 *       low half of the reference's 64-bit sort key */
+  const float* xy;              /* [P,4] (x, y, conic.x, conic.y) */
+  const float* conic_opacity;   /* [P,4] (conic.z, opacity, 1/depth, depth) */
+  const float* rgb;             /* [P,4] (r, g, b, clamped-bits) */
 } PdgsStateView;
 int pdgs_state_view(const PdgsState* state, int64_t P, int32_t width, int32_t height, PdgsStateView* view);
 

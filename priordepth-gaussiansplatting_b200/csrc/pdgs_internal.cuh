@@ -42,10 +42,9 @@ inline __host__ __device__ size_t align_up(size_t v, size_t a = 128) { return (v
 
 struct GeomView {
   Ctrl* ctrl;
-  // Per-Gaussian records in BLEND-READY form (written by K1, gathered verbatim by the blend kernels):
-  float4* gA;               // (x, y, -0.5*log2e*conic.x, -log2e*conic.y)
-  float4* gB;               // (-0.5*log2e*conic.z, log2(opacity*h), 1/depth, r)
-  float4* gC;               // (g, b, depth, clamped bits)
+  float4* gA;               // (x, y, conic.x, conic.y)
+  float4* gB;               // (conic.z, opacity*h, 1/depth, depth)
+  float4* gC;               // (r, g, b, clamped bits)
   uint32_t* tiles_touched;  // [P]
   uint2* rect;              // [P] tile rect (x0 | y0 << 16, x1 | y1 << 16); (0, 0) = culled
   uint32_t* depth_keys;     // [P] depth bits (0xffffffff = culled); sorted ascending after the depth sort
@@ -166,15 +165,6 @@ inline __host__ BinningView carve_binning(void* base, int64_t capacity) {
   v.bytes = off;
   return v;
 }
-
-// Record scaling: alpha = ex2(L + hA dx^2 + nB dx dy + hC dy^2) with hA = REC_HALF_LOG2E * conic.x, nB = REC_LOG2E *
-// conic.y, hC = REC_HALF_LOG2E * conic.z, L = log2(opacity * h); the accessors give the plain values back to K8/K9.
-constexpr float REC_LOG2E_POS = 1.4426950408889634f;
-constexpr float REC_HALF_LOG2E = -0.5f * REC_LOG2E_POS, REC_LOG2E = -REC_LOG2E_POS;
-__device__ __forceinline__ float rec_conic_a(const float4& gA) { return gA.z * (1.0f / REC_HALF_LOG2E); }
-__device__ __forceinline__ float rec_conic_b(const float4& gA) { return gA.w * (1.0f / REC_LOG2E); }
-__device__ __forceinline__ float rec_conic_c(const float4& gB) { return gB.x * (1.0f / REC_HALF_LOG2E); }
-__device__ __forceinline__ float rec_opacity(const float4& gB) { return exp2f(gB.y); }
 
 // Per-Gaussian gradient accumulator written by the backward blend (12 floats, 3 x float4):
 //   [0..3]  dmean2D.x, dmean2D.y, dconic.x, dconic.y

@@ -192,10 +192,9 @@ __global__ void __launch_bounds__(PRE_THREADS, PDGS_PRE_CTAS) preprocess_kernel(
     }
   }
   const float opacity = load_opacity(a, idx);
-  // blend-ready records (pdgs_internal.cuh GeomView): conic pre-scaled by log2(e), log2 of the effective opacity
-  g.gA[idx] = make_float4(go.px, go.py, REC_HALF_LOG2E * go.conA, REC_LOG2E * go.conB);
-  g.gB[idx] = make_float4(REC_HALF_LOG2E * go.conC, __log2f(opacity * go.h), PD_DIV(1.0f, go.depth), rgb[0]);
-  g.gC[idx] = make_float4(rgb[1], rgb[2], go.depth, __uint_as_float(clamped));
+  g.gA[idx] = make_float4(go.px, go.py, go.conA, go.conB);
+  g.gB[idx] = make_float4(go.conC, opacity * go.h, PD_DIV(1.0f, go.depth), go.depth);
+  g.gC[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
   radii[idx] = go.radius;
   g.depth_keys[idx] = __float_as_uint(go.depth);
   g.rect[idx] = make_uint2((uint32_t)go.rx0 | ((uint32_t)go.ry0 << 16), (uint32_t)go.rx1 | ((uint32_t)go.ry1 << 16));
@@ -236,7 +235,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_backward_kernel(Device
     //   a0 = (sum z dx, sum z dy, sum z dx^2, sum z dx dy), a1 = (sum z dy^2, sum z, sum w dL/dD, -), a2 = sum w dL/dC
     // with d = centre - pixel.  dL/dG = o*dL/dalpha, dG/dd = -G (A dx + B dy, C dy + B dx), dG/dconic = -0.5 G d d^T,
     // dL/do = sum G dL/dalpha = (sum z) / o.
-    const float cA = rec_conic_a(gA), cB = rec_conic_b(gA), cC = rec_conic_c(gB), o = rec_opacity(gB);
+    const float cA = gA.z, cB = gA.w, cC = gB.x, o = gB.y;
     in.g_mean2d_x = -(0.5f * (float)a.W) * (cA * a0.x + cB * a0.y);
     in.g_mean2d_y = -(0.5f * (float)a.H) * (cC * a0.y + cB * a0.x);
     in.g_conic_x = -0.5f * a0.z; in.g_conic_y = -0.5f * a0.w; in.g_conic_w = -0.5f * a1.x;
@@ -453,7 +452,7 @@ __global__ void __launch_bounds__(PB_TILE, DEFER ? PDGS_PB_DEFER_CTAS : 2) prepr
       BwdIn in;
       {
         // acc holds the raw pixel moments of z = o*G*dL/dalpha about the Gaussian's centre (pdgs_render.cu)
-        const float cA = rec_conic_a(gA), cB = rec_conic_b(gA), cC = rec_conic_c(gB), o = rec_opacity(gB);
+        const float cA = gA.z, cB = gA.w, cC = gB.x, o = gB.y;
         in.g_mean2d_x = -(0.5f * (float)a.W) * (cA * a0.x + cB * a0.y);
         in.g_mean2d_y = -(0.5f * (float)a.H) * (cC * a0.y + cB * a0.x);
         in.g_conic_x = -0.5f * a0.z; in.g_conic_y = -0.5f * a0.w; in.g_conic_w = -0.5f * a1.x;

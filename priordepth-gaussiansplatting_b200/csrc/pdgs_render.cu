@@ -2,17 +2,9 @@
 // Replaces renderCUDA (forward/backward) of the reference rasterizer (source absent;
 // SURVEY.md 2.3(b) K6/K7, A.7, A.8).
 //
-// Work item = one 8x4 pixel patch of a 16x16 tile, owned by one warp (lane = pixel).  The per-Gaussian
-// records (GeomView gA/gB/gC) are written by the preprocess kernel in BLEND-READY form -- conic pre-scaled
-// by log2(e), log2 of the opacity -- so staging a list entry is a plain 48-byte copy.
-//   forward:  one CTA per tile; batches of 256 list entries are staged by the CTA (one thread per entry,
-//             which also computes the entry's patch mask), then each warp visits its survivors.
-//   backward: every warp is AUTONOMOUS (no CTA barrier at all): it scans the patch-mask bytes the forward
-//             left per sorted pair, 32 list entries per step, and gathers only its own survivors' records
-//             with cp.async into a double-buffered per-warp ring one step ahead of the arithmetic.  In
-//             round 1 the backward staged CTA-wide behind two __syncthreads per 256 entries, and seven warps
-//             waited for the slowest at every batch (ncu r01J: 2.5 barrier stalls per issue, issue active 66 %).
-// Both kernels are instruction-issue bound, so the design removes instructions:
+// One CTA per 16x16 tile, 8 warps, each warp owns an 8x4 pixel patch.  Batches of 256 list
+// entries are staged in shared memory as three float4 records.  Both kernels are
+// instruction-issue bound (ncu r01b: issue active 87 %), so the design removes instructions:
 //
 //  * Hierarchical culling.  The thread that stages a Gaussian also tests its alpha >= 1/255
 //    footprint (the ellipse 0.5 d^T Q d <= ln(255 o)) against the eight warp patches of the tile
@@ -77,11 +69,11 @@ __device__ __forceinline__ float rcp_approx(float x) {
 // Mask of the warp patches (bit = warp index = row*2 + col; 2 columns of 8 px, 4 rows of 4 px) of the
 // tile at (tx0, ty0) that the alpha >= 1/255 footprint of a Gaussian can reach.  Conservative: the
 // threshold carries a margin far above the fp32 error of the per-pixel evaluation, and any
-// non-finite / non-positive-definite input keeps every patch.  A, B, C = conic, log2o = log2(opacity).
-__device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, float B, float C, float log2o, float tx0,
-                                               float ty0) {
-  // alpha < 1/255 everywhere iff 255 o < 1; tested with a 0.1 % margin on o: log2(0.999 / 255) = -7.995797
-  if (!(log2o >= -7.995797f)) return (log2o == log2o) ? 0u : 0xFFu;
+// non-finite / non-positive-definite input keeps every patch.
+__device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, float B, float C, float o, float log2o,
+                                               float tx0, float ty0) {
+  const float o255 = 255.0f * o;
+  if (!(o255 >= 0.999f)) return (o255 == o255) ? 0u : 0xFFu;  // alpha < 1/255 everywhere
   if (!(A > 0.f) || !(C > 0.f)) return 0xFFu;
   // ln(255 o) = (log2 o + log2 255) ln 2, with the margin
   const float tau = fmaf((log2o + 7.994353436858858f) * 0.6931471805599453f, 1.002f, 0.02f);
@@ -159,32 +151,36 @@ __device__ __forceinline__ uint32_t patch_mask(float gx, float gy, float A, floa
   return mask;
 }
 
-struct Stage {          // 49 bytes per staged list entry (forward)
-  float4 a[RT];         // x, y, -0.5*conA*log2e, -conB*log2e        (= record gA)
-  float4 b[RT];         // -0.5*conC*log2e, log2(opacity), 1/depth, r (= record gB)
-  float4 c[RT];         // g, b, -, -                                 (= record gC.xy)
+struct Stage {          // 49 bytes per staged list entry
+  float4 a[RT];         // x, y, -0.5*conA*log2e, -conB*log2e
+  float4 b[RT];         // -0.5*conC*log2e, log2(opacity), 1/depth, r
+  float4 c[RT];         // g, b, Gaussian id (bits), -
   uint8_t mask[RT];     // warp patches the Gaussian can reach
 };
 
-constexpr float INV_HALF_LOG2E = -2.0f / LOG2E;  // conic.x = INV_HALF_LOG2E * gA.z, conic.z likewise from gB.x
-constexpr float INV_LOG2E = -1.0f / LOG2E;       // conic.y = INV_LOG2E * gA.w
-
-// Forward: stage list entry `src` (or nothing when !valid) into slot threadIdx.x, compute the patch mask of the entry
-// and leave it in pair_mask[src] for the backward.
+// Stage list entry `src` (or nothing when !valid) into slot threadIdx.x.  The forward (REUSE = false) computes the
+// patch mask and leaves it in pair_mask[src]; the backward (REUSE = true) reads it back instead of recomputing it and
+// does not gather the records of an entry that reaches no patch (35 % of the pairs on C4).
+template <bool REUSE>
 __device__ __forceinline__ void stage_entry(Stage& st, bool valid, uint32_t src, const float4* __restrict__ gA,
                                             const float4* __restrict__ gB, const float4* __restrict__ gC,
                                             const uint32_t* __restrict__ point_list, uint8_t* __restrict__ pair_mask,
                                             float tx0, float ty0) {
   uint32_t m = 0;
   if (valid) {
-    const uint32_t id = __ldg(point_list + src);
-    const float4 a = __ldg(gA + id), b = __ldg(gB + id);
-    const float2 c = __ldg(reinterpret_cast<const float2*>(gC + id));
-    st.a[threadIdx.x] = a;
-    st.b[threadIdx.x] = b;
-    st.c[threadIdx.x] = make_float4(c.x, c.y, 0.f, 0.f);
-    m = patch_mask(a.x, a.y, INV_HALF_LOG2E * a.z, INV_LOG2E * a.w, INV_HALF_LOG2E * b.x, b.y, tx0, ty0);
-    pair_mask[src] = (uint8_t)m;
+    if (REUSE) m = pair_mask[src];
+    if (!REUSE || m != 0) {
+      const uint32_t id = __ldg(point_list + src);
+      const float4 a = __ldg(gA + id), b = __ldg(gB + id), c = __ldg(gC + id);
+      const float L = __log2f(b.y);
+      st.a[threadIdx.x] = make_float4(a.x, a.y, (-0.5f * LOG2E) * a.z, -LOG2E * a.w);
+      st.b[threadIdx.x] = make_float4((-0.5f * LOG2E) * b.x, L, b.z, c.x);
+      st.c[threadIdx.x] = make_float4(c.y, c.z, __uint_as_float(id), 0.f);
+      if (!REUSE) {
+        m = patch_mask(a.x, a.y, a.z, a.w, b.x, b.y, L, tx0, ty0);
+        pair_mask[src] = (uint8_t)m;
+      }
+    }
   }
   st.mask[threadIdx.x] = (uint8_t)m;
 }
@@ -238,7 +234,7 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
   bool done = !inside;
   for (uint32_t base = range.x; base < range.y; base += RT) {
     if (__syncthreads_count(done) == RT) break;
-    stage_entry(st, base + threadIdx.x < range.y, base + threadIdx.x, gA, gB, gC, point_list, pair_mask, tx0, ty0);
+    stage_entry<false>(st, base + threadIdx.x < range.y, base + threadIdx.x, gA, gB, gC, point_list, pair_mask, tx0, ty0);
     __syncthreads();
     if (__all_sync(FULL, done)) continue;  // this warp's patch is finished; it only helps staging
     const int cnt = min((uint32_t)RT, range.y - base);
@@ -329,47 +325,22 @@ __device__ __forceinline__ void sts32(uint32_t a, uint32_t x) { asm volatile("st
 #ifndef PDGS_BWD_CTAS
 #define PDGS_BWD_CTAS 4
 #endif
-#ifndef PDGS_BWD_WARPS
-#define PDGS_BWD_WARPS 8
-#endif
 constexpr int FB = PDGS_BWD_FB;   // Gaussians per phase-2 panel (8 or 16)
 constexpr int FPARTS = 32 / FB;   // lanes per panel row in phase 2; each covers FB pixels = FB/8 pixel rows of the patch
 static_assert(FB == 8 || FB == 16, "panel rows");
-constexpr int BWD_WARPS = PDGS_BWD_WARPS;  // warps per CTA; every warp is an independent (tile, patch) work item
-constexpr int BWD_THREADS = 32 * BWD_WARPS;
 
-// Per-warp shared memory of the backward (byte offsets from the warp's base):
-//   [WB_REC)   2 buffers x 32 slots x 48 B: records (gA, gB, gC) of the survivors of a 32-entry step, compacted in
-//              visiting order, filled by cp.async one step ahead
-//   [WB_META)  2 buffers x 32 x (Gaussian id, list position)
-//   [WB_PANEL) FB rows of PROW bytes: [0, 256) (z, w) of the warp's 32 pixels, [256, 264) centre of the row's
-//              Gaussian, [264, 268) its Gaussian id; then 32 x float4 (dL/dC rgb, dL/dD) of the warp's pixels.
-// PROW = 280 makes both panel access patterns conflict-free: lane = pixel writes 8-byte columns of one row, lane = row
+// Per-warp panel in dynamic shared memory (byte offsets from the warp's base):
+//   FB rows of PROW bytes: [0, 256) (z, w) of the warp's 32 pixels, [256, 264) centre of the row's Gaussian,
+//   [264, 268) its Gaussian id; then 32 x float4 (dL/dC rgb, dL/dD) of the warp's pixels.
+// PROW = 280 makes both access patterns conflict-free: lane = pixel writes 8-byte columns of one row, lane = row
 // reads one column (row stride 70 words: 6 g mod 32 is distinct and even for g = 0..15; with 8 rows the second
 // lane group of a half-warp sits 16 words further, also distinct).
-constexpr uint32_t REC_BYTES = 48, STEP = 32;
 constexpr uint32_t PROW = 280, PR_GXY = 256, PR_POS = 264;
 constexpr uint32_t WP_GPIX = FB * PROW, WP_BYTES = WP_GPIX + 32 * 16;
-constexpr uint32_t WB_REC = 0, WB_META = 2 * STEP * REC_BYTES, WB_PANEL = WB_META + 2 * STEP * 8,
-                   WB_BYTES = WB_PANEL + WP_BYTES, BWD_SMEM = BWD_WARPS * WB_BYTES;
-static_assert(PROW % 8 == 0 && WP_BYTES % 16 == 0 && WB_PANEL % 16 == 0 && WB_BYTES % 16 == 0, "panel alignment");
-
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ uint2 lds64u(uint32_t a) {
-  uint2 v;
-  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a) : "memory");
-  return v;
-}
-__device__ __forceinline__ void sts64u(uint32_t a, uint32_t x, uint32_t y) {
-  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(x), "r"(y) : "memory");
-}
+constexpr uint32_t ST_B = (uint32_t)offsetof(Stage, b), ST_C = (uint32_t)offsetof(Stage, c);
+constexpr uint32_t BWD_PANELS = (uint32_t)((sizeof(Stage) + 15) / 16 * 16), BWD_SMAX = BWD_PANELS + NWARP * WP_BYTES,
+                   BWD_SMEM = BWD_SMAX + NWARP * 4;
+static_assert(PROW % 8 == 0 && WP_BYTES % 16 == 0, "panel alignment");
 
 // Phase 2: reduce `count` panel rows to per-Gaussian sums and add them to the global accumulator.
 // wp = shared-memory address of the warp's panel.  Lane = (row g, pixel part); each lane takes raw moments of
@@ -438,12 +409,11 @@ __device__ __forceinline__ void flush_panel(uint32_t wp, int count, int lane, fl
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(BWD_THREADS, PDGS_BWD_CTAS) render_backward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
+__global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
                                                                 const float4* __restrict__ gC,
                                                                 const uint2* __restrict__ ranges,
                                                                 const uint32_t* __restrict__ point_list,
-                                                                const uint8_t* __restrict__ pair_mask, int W, int H,
-                                                                int grid_x, uint32_t n_items,
+                                                                uint8_t* __restrict__ pair_mask, int W, int H,
                                                                 const float* __restrict__ bg,
                                                                 const float* __restrict__ final_T,
                                                                 const uint32_t* __restrict__ n_contrib,
@@ -451,24 +421,19 @@ __global__ void __launch_bounds__(BWD_THREADS, PDGS_BWD_CTAS) render_backward_ke
                                                                 const float* __restrict__ dL_dinvdepth,
                                                                 float* __restrict__ acc) {
   extern __shared__ __align__(16) unsigned char bwd_smem[];
+  Stage& st = *reinterpret_cast<Stage*>(bwd_smem);
+  uint32_t* s_max = reinterpret_cast<uint32_t*>(bwd_smem + BWD_SMAX);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // work item = (tile, patch): eight consecutive items are the eight 8x4 patches of one tile
-  const uint32_t item = blockIdx.x * BWD_WARPS + warp;
-  if (item >= n_items) return;
-  const uint32_t tile = item >> 3, patch = item & 7u;
-  const int tile_x = (int)(tile % (uint32_t)grid_x), tile_y = (int)(tile / (uint32_t)grid_x);
-  const uint32_t wsm = smem_base(bwd_smem) + WB_BYTES * warp, wp = wsm + WB_PANEL;
-  const int X0 = tile_x * TILE + (int)(patch & 1u) * 8, Y0 = tile_y * TILE + (int)(patch >> 1) * 4;
+  const uint32_t sst = smem_base(bwd_smem), wp = sst + BWD_PANELS + WP_BYTES * warp;
+  const int X0 = blockIdx.x * TILE + (warp & 1) * 8, Y0 = blockIdx.y * TILE + (warp >> 1) * 4;
   const int px = X0 + (lane & 7), py = Y0 + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
-  const uint2 range = ranges[tile];
+  const float tx0 = (float)(blockIdx.x * TILE), ty0 = (float)(blockIdx.y * TILE);
+  const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   const size_t pix = (size_t)py * W + px, hw = (size_t)W * H;
   const float T_final = inside ? final_T[pix] : 0.f;
   const uint32_t last_contributor = inside ? n_contrib[pix] : 0u;
-  // this warp needs the list positions below the largest n_contrib of its own pixels only
-  const uint32_t wmax = min(__reduce_max_sync(FULL, last_contributor), range.y - range.x);
-  if (wmax == 0) return;
   float gp0 = 0.f, gp1 = 0.f, gp2 = 0.f, gpd = 0.f;
   if (inside) {
     gp0 = dL_dcolor[pix];
@@ -479,11 +444,16 @@ __global__ void __launch_bounds__(BWD_THREADS, PDGS_BWD_CTAS) render_backward_ke
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(wp + WP_GPIX + 16 * lane), "f"(gp0), "f"(gp1), "f"(gp2),
                "f"(gpd)
                : "memory");
-  const uint32_t wbit = 1u << patch;
-  const uint32_t lt_mask = (1u << lane) - 1u;
+  // the tile only needs list positions below the largest n_contrib of its pixels, each warp below its own
+  const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
+  if (lane == 0) s_max[warp] = wmax;
+  __syncthreads();
+  uint32_t todo = 0;
+#pragma unroll
+  for (int w = 0; w < NWARP; ++w) todo = max(todo, s_max[w]);
+  todo = min(todo, range.y - range.x);
+  const uint32_t wbit = 1u << warp;
   const float X0f = (float)X0, Y0f = (float)Y0;
-  const uint8_t* __restrict__ tmask = pair_mask + range.x;
-  const uint32_t* __restrict__ tlist = point_list + range.x;
 
   // Back to front.  With q_i = c_i . dL/dC + (1/z_i) dL/dD and w_i = alpha_i T_i, the reference's recurrence
   //   dL/dalpha_i = T_i (c_i - accum_rec_i) . dL/dC - T_final/(1 - alpha_i) (bg . dL/dC)
@@ -494,81 +464,63 @@ __global__ void __launch_bounds__(BWD_THREADS, PDGS_BWD_CTAS) render_backward_ke
   int slot = 0;
   uint32_t wrow = wp;  // shared address of the panel row being filled
 
-  // Step s covers list positions hi_s - lane, hi_s = wmax - 1 - 32 s (descending: lane order = visiting order).
-  // Software pipeline: while step s is processed, the records of step s + 1 are in flight (cp.async group) and the
-  // mask bytes / ids of step s + 2 are in flight (plain coalesced loads into two registers).
-  const int nsteps = (int)((wmax + STEP - 1) / STEP);
-  uint32_t m_nxt = 0, id_nxt = 0;  // patch bit and Gaussian id of this lane's entry of the NEXT step to issue
-  auto fetch = [&](int s) {
-    const int pos = (int)wmax - 1 - (int)STEP * s - lane;
-    m_nxt = 0;
-    id_nxt = 0;
-    if (s < nsteps && pos >= 0) {
-      m_nxt = (uint32_t)__ldg(tmask + pos) & wbit;
-      id_nxt = __ldg(tlist + pos);
-    }
-  };
-  // gather this lane's survivor (if any) of step s into buffer s & 1, slot = rank among the step's survivors
-  auto issue = [&](int s, uint32_t surv) {
-    if (m_nxt) {
-      const uint32_t k = (uint32_t)__popc(surv & lt_mask);
-      const uint32_t dst = wsm + WB_REC + (uint32_t)(s & 1) * (STEP * REC_BYTES) + k * REC_BYTES;
-      cp_async16(dst, gA + id_nxt);
-      cp_async16(dst + 16, gB + id_nxt);
-      cp_async16(dst + 32, gC + id_nxt);
-      sts64u(wsm + WB_META + (uint32_t)(s & 1) * (STEP * 8) + k * 8, id_nxt, (uint32_t)((int)wmax - 1 - (int)STEP * s - lane));
-    }
-    cp_async_commit();
-  };
-  fetch(0);
-  uint32_t surv_cur = __ballot_sync(FULL, m_nxt != 0);
-  issue(0, surv_cur);
-  fetch(1);
-  for (int s = 0; s < nsteps; ++s) {
-    const uint32_t surv_nxt = __ballot_sync(FULL, m_nxt != 0);  // step s + 1
-    __syncwarp();              // every lane has finished reading buffer (s + 1) & 1 (step s - 1)
-    issue(s + 1, surv_nxt);
-    fetch(s + 2);
-    cp_async_wait<1>();        // this lane's copies of step s have landed ...
-    __syncwarp();              // ... and so have every other lane's (and their meta stores)
-    const int n = __popc(surv_cur);
-    uint32_t rec = wsm + WB_REC + (uint32_t)(s & 1) * (STEP * REC_BYTES);
-    uint32_t meta = wsm + WB_META + (uint32_t)(s & 1) * (STEP * 8);
-    for (int k = 0; k < n; ++k, rec += REC_BYTES, meta += 8) {
-      const float4 a = lds128(rec), b = lds128(rec + 16);
-      const uint2 ip = lds64u(meta);  // (Gaussian id, list position)
-      const float dx = a.x - pxf, dy = a.y - pyf;
-      const float t = gauss_exponent(dx, dy, a.z, a.w, b.x, b.y);
-      const float araw = ex2_approx(t);  // o * G
-      const float alpha = fminf(ALPHA_MAX, araw);
-      const bool active = (ip.y < last_contributor) && !(t > b.y) && !(alpha < ALPHA_MIN);
-      if (__any_sync(FULL, active)) {
-        float z = 0.f, w = 0.f;
-        if (active) {
-          const float2 c = lds64(rec + 32);  // g, b
-          const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
-          T *= inv;
-          w = alpha * T;
-          float q = b.w * gp0;
-          q = fmaf(c.x, gp1, q);
-          q = fmaf(c.y, gp2, q);
-          q = fmaf(b.z, gpd, q);
-          const float dL_dalpha = fmaf(T, q, behind * inv);
-          behind = fmaf(-w, q, behind);
-          z = araw * dL_dalpha;  // = o * G * dL/dalpha; K8/K9 takes the factor o into account
-        }
-        sts64(wrow + 8 * lane, z, w);
-        sts64(wrow + PR_GXY, a.x, a.y);  // every lane stores the same words: no lane predicate, no conflict
-        sts32(wrow + PR_POS, ip.x);
-        wrow += PROW;
-        if (++slot == FB) {
-          flush_panel(wp, FB, lane, X0f, Y0f, acc);
-          slot = 0;
-          wrow = wp;
+  for (uint32_t done = 0; done < todo; done += RT) {
+    __syncthreads();
+    const uint32_t progress = done + threadIdx.x;
+    stage_entry<true>(st, progress < todo, range.x + (todo - 1 - progress), gA, gB, gC, point_list, pair_mask, tx0, ty0);
+    __syncthreads();
+    const int cnt = min((uint32_t)RT, todo - done);
+    const uint32_t top = todo - 1 - done;  // list position of staged entry 0 (entries go back to front)
+    // staged entry j sits at list position top - j; this warp needs positions < wmax only, i.e. j >= jmin
+    const int jmin = (int)top - (int)wmax + 1;
+    if (jmin >= cnt) continue;
+    for (int k = 0; k * 32 < cnt; ++k) {
+      uint32_t mw = __ballot_sync(FULL, (st.mask[k * 32 + lane] & wbit) != 0);
+      const int lo = jmin - k * 32;
+      if (lo >= 32) continue;
+      if (lo > 0) mw &= 0xffffffffu << lo;
+      uint32_t rm = __brev(mw);  // leading one = first entry to visit
+      const uint32_t last_rec = sst + 16u * (uint32_t)(k * 32 + 31);
+      const uint32_t pos_last = top - (uint32_t)(k * 32 + 31);  // list position of the block's last entry (may wrap: only used + hb)
+      while (rm) {
+        const uint32_t hb = highest_bit(rm);  // entry j = k*32 + 31 - hb
+        rm ^= 1u << hb;
+        const uint32_t rec = record_addr(last_rec, hb);
+        const float4 a = lds128(rec), b = lds128(rec + ST_B);
+        const float dx = a.x - pxf, dy = a.y - pyf;
+        const float t = gauss_exponent(dx, dy, a.z, a.w, b.x, b.y);
+        const float araw = ex2_approx(t);  // o * G
+        const float alpha = fminf(ALPHA_MAX, araw);
+        const uint32_t pos = pos_last + hb;  // = top - j
+        const bool active = (pos < last_contributor) && !(t > b.y) && !(alpha < ALPHA_MIN);
+        if (__any_sync(FULL, active)) {
+          float z = 0.f, w = 0.f;
+          const float4 c = lds128(rec + ST_C);  // uniform address: one broadcast wavefront
+          const uint32_t row_id = __float_as_uint(c.z);
+          if (active) {
+            const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
+            T *= inv;
+            w = alpha * T;
+            float q = b.w * gp0;
+            q = fmaf(c.x, gp1, q);
+            q = fmaf(c.y, gp2, q);
+            q = fmaf(b.z, gpd, q);
+            const float dL_dalpha = fmaf(T, q, behind * inv);
+            behind = fmaf(-w, q, behind);
+            z = araw * dL_dalpha;  // = o * G * dL/dalpha; K8/K9 takes the factor o into account
+          }
+          sts64(wrow + 8 * lane, z, w);
+          sts64(wrow + PR_GXY, a.x, a.y);  // every lane stores the same words: no lane predicate, no conflict
+          sts32(wrow + PR_POS, row_id);
+          wrow += PROW;
+          if (++slot == FB) {
+            flush_panel(wp, FB, lane, X0f, Y0f, acc);
+            slot = 0;
+            wrow = wp;
+          }
         }
       }
     }
-    surv_cur = surv_nxt;
   }
   if (slot > 0) flush_panel(wp, slot, lane, X0f, Y0f, acc);
 }
@@ -588,7 +540,7 @@ cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im,
 cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
                                    uint8_t* pair_mask, const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
   if (a.W <= 0 || a.H <= 0) return cudaSuccess;
-  // more than 48 KB of dynamic shared memory per CTA: opt in once per device
+  // 49.3 KB of dynamic shared memory per CTA (above the 48 KB static limit): opt in once per device
   static thread_local int configured_device = -1;
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -598,11 +550,9 @@ cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im
     if (e != cudaSuccess) return e;
     configured_device = dev;
   }
-  const uint32_t n_items = (uint32_t)a.grid_x * (uint32_t)a.grid_y * 8u;
-  const uint32_t blocks = (n_items + BWD_WARPS - 1) / BWD_WARPS;
-  render_backward_kernel<<<blocks, BWD_THREADS, BWD_SMEM, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, pair_mask, a.W, a.H,
-                                                               a.grid_x, n_items, a.bg, im.final_T, im.n_contrib, dL_dcolor,
-                                                               dL_dinvdepth, acc);
+  dim3 grid(a.grid_x, a.grid_y);
+  render_backward_kernel<<<grid, RT, BWD_SMEM, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, pair_mask, a.W, a.H, a.bg,
+                                                    im.final_T, im.n_contrib, dL_dcolor, dL_dinvdepth, acc);
   return cudaGetLastError();
 }
 

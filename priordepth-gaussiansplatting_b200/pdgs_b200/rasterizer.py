@@ -521,7 +521,7 @@ def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int, 
     conic_opacity = grab(v.conic_opacity, P * 4, torch.float32).view(-1, 4)
     rgb = grab(v.rgb, P * 4, torch.float32).view(-1, 4)
     # the reference's 64-bit sort key of every pair: (tile << 32) | depth bits of its Gaussian
-    depth32 = rgb[:, 2].contiguous().view(torch.int32)
+    depth32 = conic_opacity[:, 3].contiguous().view(torch.int32)
     depth_bits = depth32.to(torch.int64) & 0xFFFFFFFF
     sorted_keys = (sorted_tiles.to(torch.int64) << 32) | depth_bits[point_list.to(torch.int64)]
     return dict(
