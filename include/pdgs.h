@@ -171,14 +171,17 @@ int pdgs_backward(PdgsHandle* h, const PdgsScene* scene, const PdgsCamera* cam, 
  *   grad_shs[k][c]  (+)= basis_k(dir_v) * color_grads[v][c],   dir_v = normalize(mean - campos_views[v])
  *   grad_means3D    +=  d(rgb)/d(mean) through dir_v           (the view-direction term of K9)
  * color_grads: [n_views][P][3] device, campos_views: [n_views][3] device.  accumulate = 0 overwrites grad_shs
- * (grad_means3D is always added to).  Replaces n_views read-modify-writes of the [P,M,3] SH gradient by one. */
+ * (grad_means3D is always added to).  Replaces n_views read-modify-writes of the [P,M,3] SH gradient by one.
+ * first / count select the Gaussians [first, first + count) (count <= 0: all; `first` a multiple of 4, for the split
+ * variant of 256): the view-parallel step runs the pass in chunks along P and starts the all-reduce of a chunk's rows
+ * while the next chunk is computed (SURVEY 8(e) "chunking along P"). */
 int pdgs_sh_backward_views(PdgsHandle* h, const PdgsScene* scene, int32_t sh_degree, const float* campos_views,
                            const float* color_grads, int32_t n_views, float* grad_shs, float* grad_means3D,
-                           int32_t accumulate, void* stream);
+                           int32_t accumulate, int64_t first, int64_t count, void* stream);
 /* Same for a scene given as shs_dc / shs_rest: gradients go to grad_dc [P,1,3] and grad_rest [P,M-1,3]. */
 int pdgs_sh_backward_views_split(PdgsHandle* h, const PdgsScene* scene, int32_t sh_degree, const float* campos_views,
                                  const float* color_grads, int32_t n_views, float* grad_dc, float* grad_rest,
-                                 float* grad_means3D, int32_t accumulate, void* stream);
+                                 float* grad_means3D, int32_t accumulate, int64_t first, int64_t count, void* stream);
 
 /* Image-space loss of one view and its cotangents in one pass (the caller-side torch ops at
  * /root/reference/train.py:153 `l1_loss` = utils/loss_utils.py:40-41 and :174 the depth-prior term):

@@ -407,7 +407,7 @@ int pdgs_image_loss_ssim(PdgsHandle* h, const float* color, const float* target,
 
 int pdgs_sh_backward_views(PdgsHandle* h, const PdgsScene* scene, int32_t sh_degree, const float* campos_views,
                            const float* color_grads, int32_t n_views, float* grad_shs, float* grad_means3D,
-                           int32_t accumulate, void* stream) {
+                           int32_t accumulate, int64_t first, int64_t count, void* stream) {
   if (!h || !scene || !campos_views || !color_grads || n_views < 0)
     return fail(PDGS_E_INVALID, "pdgs_sh_backward_views: bad argument");
   if (scene->P <= 0 || n_views == 0) return PDGS_OK;
@@ -417,16 +417,18 @@ int pdgs_sh_backward_views(PdgsHandle* h, const PdgsScene* scene, int32_t sh_deg
     return fail(PDGS_E_INVALID, "pdgs_sh_backward_views: sh_degree needs more coefficients than shs holds");
   if (scene->M == 16 && (!aligned16(scene->shs) || (grad_shs && !aligned16(grad_shs))))
     return fail(PDGS_E_INVALID, "pdgs_sh_backward_views: shs / grad_shs must be 16-byte aligned");
+  if (count > 0 && (first < 0 || first + count > scene->P || first % 4 != 0))
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views: range outside [0, P) or `first` not a multiple of 4");
   cudaStream_t s = (cudaStream_t)stream;
   StageTimer t(h, PDGS_STAGE_SH_BWD, s);
   PD_CUDA(launch_sh_backward_views(scene->means3D, scene->shs, nullptr, nullptr, scene->P, scene->M, sh_degree, campos_views,
-                                   color_grads, n_views, grad_shs, nullptr, nullptr, grad_means3D, accumulate, s));
+                                   color_grads, n_views, grad_shs, nullptr, nullptr, grad_means3D, accumulate, first, count, s));
   return PDGS_OK;
 }
 
 int pdgs_sh_backward_views_split(PdgsHandle* h, const PdgsScene* scene, int32_t sh_degree, const float* campos_views,
                                  const float* color_grads, int32_t n_views, float* grad_dc, float* grad_rest,
-                                 float* grad_means3D, int32_t accumulate, void* stream) {
+                                 float* grad_means3D, int32_t accumulate, int64_t first, int64_t count, void* stream) {
   if (!h || !scene || !campos_views || !color_grads || n_views < 0)
     return fail(PDGS_E_INVALID, "pdgs_sh_backward_views_split: bad argument");
   if (scene->P <= 0 || n_views == 0) return PDGS_OK;
@@ -439,10 +441,13 @@ int pdgs_sh_backward_views_split(PdgsHandle* h, const PdgsScene* scene, int32_t 
   if (!aligned16(scene->shs_dc) || (scene->shs_rest && !aligned16(scene->shs_rest)) || (grad_dc && !aligned16(grad_dc)) ||
       (grad_rest && !aligned16(grad_rest)))
     return fail(PDGS_E_INVALID, "pdgs_sh_backward_views_split: SH arrays must be 16-byte aligned");
+  if (count > 0 && (first < 0 || first + count > scene->P || first % 256 != 0))
+    return fail(PDGS_E_INVALID, "pdgs_sh_backward_views_split: range outside [0, P) or `first` not a multiple of 256");
   cudaStream_t s = (cudaStream_t)stream;
   StageTimer t(h, PDGS_STAGE_SH_BWD, s);
   PD_CUDA(launch_sh_backward_views(scene->means3D, nullptr, scene->shs_dc, scene->shs_rest, scene->P, scene->M, sh_degree,
-                                   campos_views, color_grads, n_views, nullptr, grad_dc, grad_rest, grad_means3D, accumulate, s));
+                                   campos_views, color_grads, n_views, nullptr, grad_dc, grad_rest, grad_means3D, accumulate,
+                                   first, count, s));
   return PDGS_OK;
 }
 

@@ -219,7 +219,7 @@ cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const in
 cudaError_t launch_sh_backward_views(const float* means3D, const float* shs, const float* shs_dc, const float* shs_rest,
                                      int64_t P, int M, int sh_degree, const float* campos_views, const float* color_grads,
                                      int n_views, float* grad_shs, float* grad_dc, float* grad_rest, float* grad_means3D,
-                                     int accumulate, cudaStream_t s);
+                                     int accumulate, int64_t first, int64_t count, cudaStream_t s);
 // alpha / clamp01: the loss sees clamp(color, 0, 1) * alpha (alpha: one [H*W] plane or NULL), see pdgs_loss.cu
 cudaError_t launch_image_loss(const float* color, const float* target, const float* invdepth, const float* prior,
                               const float* mask, const float* alpha, int clamp01, int W, int H, float w_color,

@@ -626,8 +626,8 @@ constexpr int SHV_VB = 8;          // views whose colour gradients are in flight
 
 template <int MT>  // MT = 16: fully unrolled register path; MT = 0: any M through global memory
 __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_kernel(const float* __restrict__ means3D,
-                                                                        const float* __restrict__ shs, int64_t P, int M,
-                                                                        int sh_degree,
+                                                                        const float* __restrict__ shs, int64_t P,
+                                                                        int64_t cg_stride, int M, int sh_degree,
                                                                         const float* __restrict__ campos_views,
                                                                         const float* __restrict__ color_grads,
                                                                         int n_views, float* __restrict__ grad_shs,
@@ -659,7 +659,7 @@ __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_kernel(const fl
 #pragma unroll
       for (int u = 0; u < SHV_VB; ++u) {
         const int v = (v0 + u < n_views) ? v0 + u : n_views - 1;
-        const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
+        const float* gsrc = color_grads + ((size_t)v * cg_stride + idx) * 3;
         gb[u][0] = __ldg(gsrc); gb[u][1] = __ldg(gsrc + 1); gb[u][2] = __ldg(gsrc + 2);
       }
 #pragma unroll
@@ -695,7 +695,7 @@ __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_kernel(const fl
     if (dst && !accumulate)
       for (int k = 0; k < 3 * M; ++k) dst[k] = 0.f;
     for (int v = 0; v < n_views; ++v) {
-      const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
+      const float* gsrc = color_grads + ((size_t)v * cg_stride + idx) * 3;
       const float g[3] = {__ldg(gsrc), __ldg(gsrc + 1), __ldg(gsrc + 2)};
       if (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f) continue;
       float gdir[3], basis[16];
@@ -717,8 +717,8 @@ __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_kernel(const fl
 // (odd stride, conflict-free), leaves the row's gradient in the same place and the CTA writes the span back coalesced.
 template <int MT>
 __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_split_kernel(
-    const float* __restrict__ means3D, const float* __restrict__ shs_dc, const float* __restrict__ shs_rest, int64_t P, int M,
-    int sh_degree, const float* __restrict__ campos_views, const float* __restrict__ color_grads, int n_views,
+    const float* __restrict__ means3D, const float* __restrict__ shs_dc, const float* __restrict__ shs_rest, int64_t P,
+    int64_t cg_stride, int M, int sh_degree, const float* __restrict__ campos_views, const float* __restrict__ color_grads, int n_views,
     float* __restrict__ grad_dc, float* __restrict__ grad_rest, float* __restrict__ grad_means3D, int accumulate) {
   __shared__ float s_cam[SHV_MAX_VIEWS * 3];
   __shared__ __align__(16) float s_rest[MT == 16 ? SHV_THREADS * SPLIT_REST : 4];
@@ -757,7 +757,7 @@ __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_split_kernel(
 #pragma unroll
         for (int u = 0; u < SHV_VB; ++u) {
           const int v = (v0 + u < n_views) ? v0 + u : n_views - 1;
-          const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
+          const float* gsrc = color_grads + ((size_t)v * cg_stride + idx) * 3;
           gb[u][0] = __ldg(gsrc); gb[u][1] = __ldg(gsrc + 1); gb[u][2] = __ldg(gsrc + 2);
         }
 #pragma unroll
@@ -813,7 +813,7 @@ __global__ void __launch_bounds__(SHV_THREADS) sh_backward_views_split_kernel(
       if (drest) for (int k = 0; k < rrow; ++k) drest[k] = 0.f;
     }
     for (int v = 0; v < n_views; ++v) {
-      const float* gsrc = color_grads + ((size_t)v * P + idx) * 3;
+      const float* gsrc = color_grads + ((size_t)v * cg_stride + idx) * 3;
       const float g[3] = {__ldg(gsrc), __ldg(gsrc + 1), __ldg(gsrc + 2)};
       if (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f) continue;
       float gdir[3], basis[16];
@@ -896,30 +896,44 @@ cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const in
   return cudaGetLastError();
 }
 
+// Gaussians [first, first + count) of a scene of P Gaussians (count <= 0: all of them).  color_grads is [n_views][P][3];
+// every other array is indexed by Gaussian, so a range is the same kernel on offset pointers with the view stride P.
 cudaError_t launch_sh_backward_views(const float* means3D, const float* shs, const float* shs_dc, const float* shs_rest,
                                      int64_t P, int M, int sh_degree, const float* campos_views, const float* color_grads,
                                      int n_views, float* grad_shs, float* grad_dc, float* grad_rest, float* grad_means3D,
-                                     int accumulate, cudaStream_t s) {
+                                     int accumulate, int64_t first, int64_t count, cudaStream_t s) {
   if (P <= 0 || n_views <= 0) return cudaSuccess;
-  const unsigned blocks = (unsigned)((P + SHV_THREADS - 1) / SHV_THREADS);
+  if (count <= 0) { first = 0; count = P; }
+  if (first < 0 || first + count > P) return cudaErrorInvalidValue;
+  const int rest = 3 * (M - 1);
+  means3D += 3 * first;
+  if (shs) shs += (size_t)first * 3 * M;
+  if (shs_dc) shs_dc += 3 * first;
+  if (shs_rest) shs_rest += (size_t)first * rest;
+  if (grad_shs) grad_shs += (size_t)first * 3 * M;
+  if (grad_dc) grad_dc += 3 * first;
+  if (grad_rest) grad_rest += (size_t)first * rest;
+  if (grad_means3D) grad_means3D += 3 * first;
+  color_grads += 3 * first;
+  const unsigned blocks = (unsigned)((count + SHV_THREADS - 1) / SHV_THREADS);
   for (int v0 = 0; v0 < n_views; v0 += SHV_MAX_VIEWS) {  // later chunks always add to what the first one wrote
     const int nv = (n_views - v0 < SHV_MAX_VIEWS) ? n_views - v0 : SHV_MAX_VIEWS;
     const int acc = (v0 == 0) ? accumulate : 1;
     const float* cg = color_grads + (size_t)v0 * P * 3;
     if (!shs && M == 16)
-      sh_backward_views_split_kernel<16><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs_dc, shs_rest, P, M, sh_degree,
+      sh_backward_views_split_kernel<16><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs_dc, shs_rest, count, P, M, sh_degree,
                                                                         campos_views + 3 * v0, cg, nv, grad_dc, grad_rest,
                                                                         grad_means3D, acc);
     else if (!shs)
-      sh_backward_views_split_kernel<0><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs_dc, shs_rest, P, M, sh_degree,
+      sh_backward_views_split_kernel<0><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs_dc, shs_rest, count, P, M, sh_degree,
                                                                        campos_views + 3 * v0, cg, nv, grad_dc, grad_rest,
                                                                        grad_means3D, acc);
     else if (M == 16)
-      sh_backward_views_kernel<16><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs, P, M, sh_degree, campos_views + 3 * v0, cg,
-                                                                  nv, grad_shs, grad_means3D, acc);
+      sh_backward_views_kernel<16><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs, count, P, M, sh_degree, campos_views + 3 * v0,
+                                                                  cg, nv, grad_shs, grad_means3D, acc);
     else
-      sh_backward_views_kernel<0><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs, P, M, sh_degree, campos_views + 3 * v0, cg,
-                                                                 nv, grad_shs, grad_means3D, acc);
+      sh_backward_views_kernel<0><<<blocks, SHV_THREADS, 0, s>>>(means3D, shs, count, P, M, sh_degree, campos_views + 3 * v0,
+                                                                 cg, nv, grad_shs, grad_means3D, acc);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
   }

@@ -84,9 +84,10 @@ SYMBOLS = {
                                C.POINTER(PdgsForwardOut), C.c_int32, C.POINTER(C.c_int64), vp]),
     "pdgs_backward": (C.c_int, [vp, C.POINTER(PdgsScene), C.POINTER(PdgsCamera), C.POINTER(PdgsState), vp,
                                 C.c_int64, vp, vp, vp, C.c_size_t, C.POINTER(PdgsGrads), vp]),
-    "pdgs_sh_backward_views": (C.c_int, [vp, C.POINTER(PdgsScene), C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int32, vp]),
+    "pdgs_sh_backward_views": (C.c_int, [vp, C.POINTER(PdgsScene), C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int32, C.c_int64,
+                                         C.c_int64, vp]),
     "pdgs_sh_backward_views_split": (C.c_int, [vp, C.POINTER(PdgsScene), C.c_int32, vp, vp, C.c_int32, vp, vp, vp, C.c_int32,
-                                               vp]),
+                                               C.c_int64, C.c_int64, vp]),
     "pdgs_sparse_adam": (C.c_int, [vp, C.POINTER(PdgsAdamGroup), C.c_int32, vp, vp, C.c_int64, C.c_double, C.c_double, C.c_double,
                                    C.c_int32, vp]),
     "pdgs_mark_visible": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp]),

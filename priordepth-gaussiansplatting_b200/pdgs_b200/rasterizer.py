@@ -278,9 +278,10 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors_precomp, opacities, 
 
 
 def sh_backward_views_split(means3D, dc, rest, sh_degree, campos_views, color_grads, grad_dc, grad_rest, grad_means3D,
-                            accumulate=True):
+                            accumulate=True, first=0, count=0):
     """sh_backward_views for a scene given as features_dc [P,1,3] / features_rest [P,M-1,3]
-    (C ABI pdgs_sh_backward_views_split)."""
+    (C ABI pdgs_sh_backward_views_split).  first / count: Gaussians [first, first + count) only (count 0 = all;
+    `first` a multiple of 256)."""
     lib = L.lib()
     dev = means3D.device
     if not means3D.is_cuda:
@@ -296,15 +297,17 @@ def sh_backward_views_split(means3D, dc, rest, sh_degree, campos_views, color_gr
         sc = _scene(P, means3D, rest, None, None, None, None, None, dc)
         L.check(lib.pdgs_sh_backward_views_split(h, C.byref(sc), int(sh_degree), _ptr(campos_views), _ptr(color_grads), V,
                                                  _ptr(grad_dc), _ptr(grad_rest), _ptr(grad_means3D), int(bool(accumulate)),
-                                                 stream), "pdgs_sh_backward_views_split")
+                                                 int(first), int(count), stream), "pdgs_sh_backward_views_split")
         LAUNCHES.sh_bwd = (V + 255) // 256
     return grad_dc, grad_rest, grad_means3D
 
 
-def sh_backward_views(means3D, sh, sh_degree, campos_views, color_grads, grad_shs, grad_means3D, accumulate=True):
+def sh_backward_views(means3D, sh, sh_degree, campos_views, color_grads, grad_shs, grad_means3D, accumulate=True,
+                      first=0, count=0):
     """SH part of the backward for a batch of views at once (C ABI pdgs_sh_backward_views): reads `color_grads`
     [V,P,3] (what backward left in accumulate_into["color_grad_view"] per view) and `campos_views` [V,3]; writes
-    or accumulates grad_shs [P,M,3] and adds the view-direction term to grad_means3D [P,3]."""
+    or accumulates grad_shs [P,M,3] and adds the view-direction term to grad_means3D [P,3].  first / count: Gaussians
+    [first, first + count) only (count 0 = all; `first` a multiple of 4)."""
     lib = L.lib()
     dev = means3D.device
     if not means3D.is_cuda:
@@ -319,8 +322,8 @@ def sh_backward_views(means3D, sh, sh_degree, campos_views, color_grads, grad_sh
         stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         sc = _scene(P, means3D, sh, None, None, None, None, None)
         L.check(lib.pdgs_sh_backward_views(h, C.byref(sc), int(sh_degree), _ptr(campos_views), _ptr(color_grads), V,
-                                           _ptr(grad_shs), _ptr(grad_means3D), int(bool(accumulate)), stream),
-                "pdgs_sh_backward_views")
+                                           _ptr(grad_shs), _ptr(grad_means3D), int(bool(accumulate)), int(first), int(count),
+                                           stream), "pdgs_sh_backward_views")
         LAUNCHES.sh_bwd = (V + 255) // 256
     return grad_shs, grad_means3D
 

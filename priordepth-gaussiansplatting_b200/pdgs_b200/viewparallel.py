@@ -98,6 +98,21 @@ class GradBuffer:
         dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
         dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=group)
 
+    def tail_slice(self) -> torch.Tensor:
+        """The contiguous part of the flat buffer behind the SH gradient: opacities | scales | rotations | densify
+        statistics (10 floats per Gaussian).  Nothing writes it after the last view's preprocess backward."""
+        return self.flat[self._spans["opacities"][0]:]
+
+    def row_slices(self, lo: int, hi: int, split: bool) -> List[torch.Tensor]:
+        """Flat slices holding rows [lo, hi) of the segments the deferred SH backward writes: means3D and the SH
+        gradient (packed, or features_dc + features_rest)."""
+        out = []
+        for name in ("means3D",) + (("shs_dc", "shs_rest") if split else ("shs",)):
+            off, n, w = self._spans[name]
+            if w > 0 and hi > lo:
+                out.append(self.flat[off + lo * w: off + hi * w])
+        return out
+
     @property
     def floats_per_gaussian(self) -> int:
         return sum((3 * (self.M - 1) if w is None else w) for _, w in _SEGMENTS)
@@ -169,6 +184,8 @@ class ViewParallelRasterizer:
         self._count_lock = threading.Lock()
         self._copy_stream = None
         self._color_grads = None
+        # chunks along P of the deferred SH backward when its rows are all-reduced behind it (world > 1); PDGS_REDUCE_CHUNKS
+        self.reduce_chunks = max(1, int(os.environ.get("PDGS_REDUCE_CHUNKS", "4")))
 
     def _upload(self, i, targets, priors, masks, alphas=None):
         items = [targets[i], None if priors is None else priors.get(i), None if masks is None else masks.get(i),
@@ -292,7 +309,8 @@ class ViewParallelRasterizer:
                         t.record_stream(cur)
         my = shard_views(len(views), self.rank, self.world)
         split = gaussians.get("shs_dc") is not None
-        defer = self.backend is _cuda_view_backend and (split or gaussians.get("shs") is not None) and len(my) > 0
+        sh_scene = self.backend is _cuda_view_backend and (split or gaussians.get("shs") is not None)
+        defer = sh_scene and len(my) > 0
         self.buf.zero_(skip_sh=defer)  # with the deferred SH backward every SH gradient row is written, not added to
         self.loss_acc.zero_()
         acc = self.buf.accumulate_dict(split)
@@ -370,18 +388,46 @@ class ViewParallelRasterizer:
             self.last_num_rendered.append(int(r.get("num_rendered", 0)))
             if keep_outputs:
                 outs.append(r)
-        if defer:
+        # the sequence of collectives must not depend on how many views THIS rank has (a rank without views still takes
+        # part in every all-reduce, with zero rows)
+        overlap = sh_scene and reduce and self.world > 1
+        works = []
+        if overlap:
+            # Everything behind the SH gradient (opacities, scales, rotations, densification statistics: 10 of the 61
+            # floats per Gaussian) is final once the last view's preprocess backward has run: its all-reduce starts
+            # now, on NCCL's stream, and runs while the deferred SH backward computes.
+            works.append(dist.all_reduce(self.buf.tail_slice(), op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+            works.append(dist.all_reduce(self.buf.max_radii2D, op=dist.ReduceOp.MAX, group=self.group, async_op=True))
+            works.append(dist.all_reduce(self.loss_acc, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        if defer or overlap:
             from . import rasterizer as rz
-            campos = torch.stack([views[i].campos.reshape(3) for i in my]).to(self.device, torch.float32)
-            if split:
-                rz.sh_backward_views_split(gaussians["means3D"], gaussians["shs_dc"], gaussians.get("shs_rest"),
-                                           views[my[0]].sh_degree, campos, self._color_grads, acc["shs_dc"],
-                                           acc["shs_rest"], acc["means3D"], accumulate=False)
-            else:
-                rz.sh_backward_views(gaussians["means3D"], gaussians["shs"], views[my[0]].sh_degree, campos,
-                                     self._color_grads, acc["shs"], acc["means3D"], accumulate=False)
-            self.last_launches += rz.LAUNCHES.sh_bwd
-        if reduce and self.world > 1:
+            campos = torch.stack([views[i].campos.reshape(3) for i in my]).to(self.device, torch.float32) if defer else None
+            # The SH pass runs in chunks along P: rows [lo, hi) of means3D and of the SH gradient are final
+            # when their chunk is done, so their all-reduce overlaps the next chunk's kernel.
+            P = self.buf.P
+            n_chunks = self.reduce_chunks if overlap else 1
+            step_rows = max(256, (-(-P // n_chunks) + 255) // 256 * 256)
+            for lo in range(0, max(P, 1), step_rows):
+                hi = min(P, lo + step_rows)
+                if not defer:
+                    pass  # no local view: rows stay zero, the collectives below still run
+                elif split:
+                    rz.sh_backward_views_split(gaussians["means3D"], gaussians["shs_dc"], gaussians.get("shs_rest"),
+                                               views[my[0]].sh_degree, campos, self._color_grads, acc["shs_dc"],
+                                               acc["shs_rest"], acc["means3D"], accumulate=False, first=lo, count=hi - lo)
+                else:
+                    rz.sh_backward_views(gaussians["means3D"], gaussians["shs"], views[my[0]].sh_degree, campos,
+                                         self._color_grads, acc["shs"], acc["means3D"], accumulate=False, first=lo,
+                                         count=hi - lo)
+                if defer:
+                    self.last_launches += rz.LAUNCHES.sh_bwd
+                if overlap:
+                    for t in self.buf.row_slices(lo, hi, split):
+                        works.append(dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        if overlap:
+            for w in works:
+                w.wait()  # the current stream waits for the collective; the host does not block
+        elif reduce and self.world > 1:
             self.buf.all_reduce(self.group)
             dist.all_reduce(self.loss_acc, op=dist.ReduceOp.SUM, group=self.group)
         prefetched = None

@@ -235,3 +235,40 @@ def test_deferred_sh_backward_and_accumulating_k9_against_oracle(split):
         assert helpers.elem_err(got, want[k].reshape(got.shape), floor_frac=1e-2) <= 0.05, k
     assert helpers.rel_err(buf.view("densify_grad_accum"), accum_ref) <= 1e-3
     assert torch.equal(buf.view("densify_denom").cpu(), denom_ref)
+
+
+@pytest.mark.parametrize("split", [False, True])
+def test_sh_backward_views_in_chunks_along_p_equals_one_pass(split):
+    """pdgs_sh_backward_views(_split) over [first, first + count) ranges -- what the multi-GPU step runs so that the
+    all-reduce of a chunk's rows overlaps the next chunk -- writes bit-identical rows to the single whole-P pass."""
+    from pdgs_b200 import rasterizer as rz
+    P, V = 2600, 5
+    gen = torch.Generator().manual_seed(12)
+    means = torch.randn(P, 3, generator=gen).to(DEV)
+    shs = torch.randn(P, 16, 3, generator=gen).to(DEV)
+    dc, rest = shs[:, :1].contiguous(), shs[:, 1:].contiguous()
+    campos = (3.0 * torch.randn(V, 3, generator=gen)).to(DEV)
+    cg = torch.randn(V, P, 3, generator=gen).to(DEV)
+    cg[:, ::7] = 0.0   # culled rows
+
+    def run(chunks):
+        g_sh = torch.full((P, 16, 3), 7.0, device=DEV)
+        g_dc, g_rest = torch.full((P, 1, 3), 7.0, device=DEV), torch.full((P, 15, 3), 7.0, device=DEV)
+        g_m = torch.ones(P, 3, device=DEV)
+        for lo, hi in chunks:
+            if split:
+                rz.sh_backward_views_split(means, dc, rest, 3, campos, cg, g_dc, g_rest, g_m, accumulate=False, first=lo,
+                                           count=hi - lo)
+            else:
+                rz.sh_backward_views(means, shs, 3, campos, cg, g_sh, g_m, accumulate=False, first=lo, count=hi - lo)
+        return (torch.cat([g_dc, g_rest], dim=1) if split else g_sh), g_m
+
+    whole = run([(0, 0)])
+    parts = run([(0, 1024), (1024, 2304), (2304, P)])
+    assert torch.equal(whole[0], parts[0]) and torch.equal(whole[1], parts[1])
+    assert float((whole[0] - 7.0).abs().max()) > 0.0
+    only = run([(1024, 2304)])   # rows outside the range are untouched
+    assert bool((only[0][:1024] == 7.0).all()) and bool((only[0][2304:] == 7.0).all()) and bool((only[1][:1024] == 1.0).all())
+    assert torch.equal(only[0][1024:2304], whole[0][1024:2304])
+    with pytest.raises(Exception, match="multiple"):
+        run([(10, 300)])

@@ -23,6 +23,23 @@ def test_shard_views_partitions_contiguously():
             assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
 
 
+def test_overlapped_reduce_slices_cover_the_buffer_once():
+    """The chunked multi-GPU reduce all-reduces tail_slice() plus, per chunk of rows, row_slices(lo, hi): together they
+    must cover every float of the flat gradient buffer exactly once (padding words aside)."""
+    for P, split in ((1000, False), (1000, True), (777, False), (5, True)):
+        b = GradBuffer(P, 16, "cpu")
+        b.flat.zero_()
+        b.tail_slice().add_(1.0)
+        step = 256
+        for lo in range(0, P, step):
+            for t in b.row_slices(lo, min(P, lo + step), split):
+                t.add_(1.0)
+        for name, t in b.accumulate_dict(split).items():
+            if name != "max_radii2D":
+                assert bool((t == 1.0).all()), (P, split, name)
+        assert float(b.flat.max()) == 1.0
+
+
 def test_parameter_upload_shares_cover_the_tensor():
     from pdgs_b200.viewparallel import shard_span
     for numel in (0, 1, 7, 48, 9_000_001):
