@@ -228,12 +228,17 @@ def _pct(xs, q):
     return xs[min(len(xs) - 1, max(0, int(round(q * (len(xs) - 1)))))]
 
 
-def dropin_row(args, scene, dev, iters=50, warmup=10):
+def dropin_row(args, scene, dev, iters=50, warmup=10, vary_r=False):
     """SURVEY 8(d) timing protocol on the DROP-IN API: `GaussianRasterizer.forward` + `loss.backward()` of the caller's
     loss `|clamp(render, 0, 1) - gt|.mean()` (torch ops, as /root/reference/gaussian_renderer/__init__.py:121 and
     train.py:153 do), one view per iteration cycling through the cameras, CUDA events, 10 warm-up + 50 timed,
-    median / p10 / p90.  Honours CUDA_LAUNCH_BLOCKING from the environment (the reference sets it, train.py:65)."""
+    median / p10 / p90.  Honours CUDA_LAUNCH_BLOCKING from the environment (the reference sets it, train.py:65).
+    vary_r: every other camera is a 2x zoom of an orbit camera (about 3x the pairs) and the cameras are visited in a
+    seeded random order, as a training loop pops them (train.py:130-135), so the speculative binning capacity is
+    exercised with a pair count that jumps by more than 2x between calls; misses are counted."""
+    import random
     from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    from pdgs_b200 import rasterizer as rz
     from pdgs_b200 import scenes
     torch.cuda.set_device(dev)
     lv = {k: getattr(scene, k).to(dev).requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
@@ -242,6 +247,9 @@ def dropin_row(args, scene, dev, iters=50, warmup=10):
     rast, tgts = [], []
     for i in range(n):
         v = scene.views[i]
+        if vary_r and i % 2 == 1:   # same pose, half the field of view
+            w2c = v.world_view_transform.transpose(0, 1).double().numpy()
+            v = scenes.make_view(w2c, v.image_width, v.image_height, tanx=0.3125)
         rs = GaussianRasterizationSettings(
             image_height=v.image_height, image_width=v.image_width, tanfovx=v.tanfovx, tanfovy=v.tanfovy, bg=scene.bg.to(dev),
             scale_modifier=1.0, viewmatrix=v.world_view_transform.to(dev), projmatrix=v.full_proj_transform.to(dev),
@@ -249,12 +257,14 @@ def dropin_row(args, scene, dev, iters=50, warmup=10):
         rast.append(GaussianRasterizer(raster_settings=rs))
         gen = torch.Generator().manual_seed(scenes.SEED0 + 1000 + i)
         tgts.append(torch.rand(3, v.image_height, v.image_width, generator=gen).to(dev))
-    fwd, tot = [], []
+    fwd, tot, pairs = [], [], []
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    rng = random.Random(7)
+    rz.binning_stats(reset=True)
     for it in range(warmup + iters):
         for t in list(lv.values()) + [means2D]:
             t.grad = None
-        k = it % n
+        k = rng.randrange(n) if vary_r else it % n
         ev[0].record()
         color, radii, invd = rast[k](means3D=lv["means3D"], means2D=means2D, opacities=lv["opacities"], shs=lv["shs"],
                                      scales=lv["scales"], rotations=lv["rotations"])
@@ -266,7 +276,10 @@ def dropin_row(args, scene, dev, iters=50, warmup=10):
         if it >= warmup:
             fwd.append(ev[0].elapsed_time(ev[1]))
             tot.append(ev[0].elapsed_time(ev[2]))
-    return dict(api="diff_gaussian_rasterization.GaussianRasterizer.forward + loss.backward() (torch clamp + L1 loss), one view "
+            pairs.append(int(color.grad_fn.num_rendered))
+        elif it == warmup - 1:
+            rz.binning_stats(reset=True)
+    return dict(binning=rz.binning_stats(), pairs=dict(min=min(pairs), max=max(pairs)), api="diff_gaussian_rasterization.GaussianRasterizer.forward + loss.backward() (torch clamp + L1 loss), one view "
                     "per call", iters=iters, warmup=warmup, cuda_launch_blocking=os.environ.get("CUDA_LAUNCH_BLOCKING", "") == "1",
                 fwd_ms=dict(median=_pct(fwd, 0.5), p10=_pct(fwd, 0.1), p90=_pct(fwd, 0.9)),
                 fwd_bwd_ms=dict(median=_pct(tot, 0.5), p10=_pct(tot, 0.1), p90=_pct(tot, 0.9)),
@@ -439,6 +452,7 @@ def main():
     barrier()
     clocks = stop_clock_sampler(sampler, sampler_path) if rank == 0 else None
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    binning = rz.binning_stats()              # warm-up + timed region of the batch path (this rank)
     checksum = grad_checksum(vp.buf)          # of the last timed step's all-reduced gradients (identical on all ranks)
     loss_sums_resident = [float(v) for v in vp.loss_acc.cpu()]
     # Per-stage durations (roofline / stages): a second measured region of the same steps with ONE view in flight.  In
@@ -638,7 +652,8 @@ def main():
     if world == 1 and not args.no_dropin:
         del vp
         torch.cuda.empty_cache()
-        dropin = dict(default=dropin_row(args, scene, dev), launch_blocking=dropin_row_blocking(args))
+        dropin = dict(default=dropin_row(args, scene, dev), varied_r=dropin_row(args, scene, dev, vary_r=True),
+                      launch_blocking=dropin_row_blocking(args))
 
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
@@ -649,7 +664,7 @@ def main():
                 higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
                 config=workload_config(args, scene, world), clocks=clocks, e2e=e2e, gpu_launches=launches,
                 roofline=roofline, stages=stages, cpu_baseline=cpu_baseline, library_baselines=lib, dropin=dropin,
-                grad_checksum=checksum, loss_sums=loss_sums_resident,
+                grad_checksum=checksum, loss_sums=loss_sums_resident, binning=binning,
                 stage_timing=dict(lanes=1, ms_per_step=ms_one_lane,
                                   note="stages / roofline come from a second measured region of the same steps with one view "
                                        "in flight; `value` is measured with config.lanes views in flight on separate streams"),

@@ -17,8 +17,23 @@ import torch
 
 from . import _lib as L
 
-# per-device speculative capacity of the binning buffer (pairs); follows the last pair count
+# Speculative capacity of the binning buffer (pairs) per (device, image width, image height): a HIGH-WATER MARK of the
+# pair counts seen, decaying by 1 % per call, so that a training loop that pops cameras in random order
+# (/root/reference/train.py:130-135: R varies from view to view) does not miss every time R grows.  A miss costs a
+# re-allocation and a second pass of duplicate + sort + blend; misses are counted (binning_stats()).
 _capacity_hint = {}
+_CAP_HEADROOM, _CAP_DECAY = 1.25, 0.99
+_binning_stats = {"calls": 0, "misses": 0, "sizing_calls": 0}
+
+
+def binning_stats(reset: bool = False) -> dict:
+    """{"calls", "misses", "sizing_calls"}: forwards run, forwards whose speculative binning capacity was too small
+    (duplicate + sort + blend ran twice), forwards that had no capacity hint yet (scan only, then the real pass)."""
+    out = dict(_binning_stats)
+    if reset:
+        for k in _binning_stats:
+            _binning_stats[k] = 0
+    return out
 
 
 class _Launches(threading.local):
@@ -150,7 +165,9 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
         radii = torch.empty(P, dtype=torch.int32, device=dev)
         geom = torch.empty(lib.pdgs_geom_bytes(P), **u8)
         image = torch.empty(lib.pdgs_image_bytes(W, H), **u8)
-        cap = int(_capacity_hint.get(dev, 0)) if P > 0 else 0
+        hint_key = (dev, W, H)
+        hwm = float(_capacity_hint.get(hint_key, 0.0))
+        cap = (int(hwm * _CAP_HEADROOM) + 4096) if (P > 0 and hwm > 0) else 0
         binning = None
         if cap > 0:
             binning = torch.empty(lib.pdgs_binning_bytes(cap, P), **u8)
@@ -169,15 +186,17 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
         per_bin = 1 + 2 + _passes(tiles) + 1 + 1           # scan + duplicate, 2 histograms, radix passes (4 depth + tile id), ranges, blend
         if cap > 0:
             launches += per_bin
+        _binning_stats["calls"] += 1
         if rc == L.PDGS_NEED_BINNING:
-            cap = max(int(R.value * 1.25) + 4096, 4096)
+            _binning_stats["misses" if cap > 0 else "sizing_calls"] += 1
+            cap = max(int(R.value * _CAP_HEADROOM) + 4096, 4096)
             binning = torch.empty(lib.pdgs_binning_bytes(cap, P), **u8)
             st = _state(geom, image, binning, cap)
             L.check(lib.pdgs_forward(h, C.byref(sc), C.byref(cam), C.byref(st), C.byref(out), 1, C.byref(R), stream),
                     "pdgs_forward(resume)")
             launches += per_bin
         if P > 0:
-            _capacity_hint[dev] = max(int(R.value * 1.25) + 4096, 4096)
+            _capacity_hint[hint_key] = max(float(R.value), hwm * _CAP_DECAY, 1.0)
         if binning is None:
             binning = torch.empty(0, **u8)
         binning._pdgs_capacity = cap

@@ -192,13 +192,15 @@ def test_capacity_overflow_resume_guarded(guarded):
     sc = ragged_scene(5003, 641, 359)
     view = sc.views[0]
     ref = fwd_bwd(sc, view)
-    dev = torch.device(DEV)
-    hint = rz._capacity_hint[dev]
+    key = (torch.device(DEV), view.image_width, view.image_height)
+    hint = rz._capacity_hint[key]
     assert hint > 6000
-    rz._capacity_hint[dev] = 1500
+    rz._capacity_hint[key] = 1200.0    # capacity 1200 * 1.25 + 4096 pairs: far below this view's pair count
+    misses = rz.binning_stats()["misses"]
     out = fwd_bwd(sc, view)
     guarded.check()
-    assert rz._capacity_hint[dev] == hint
+    assert rz.binning_stats()["misses"] == misses + 1
+    assert rz._capacity_hint[key] == hint
     assert torch.equal(out[1], ref[1]) and torch.equal(out[0], ref[0]) and torch.equal(out[2], ref[2])
     for k in ref[3]:
         assert helpers.rel_err(out[3][k], ref[3][k]) < 1e-4, k

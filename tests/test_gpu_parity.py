@@ -271,13 +271,26 @@ def test_binning_capacity_regrow_and_speculative_paths_agree():
     small = scenes.camera_relative_scene("s", 21, 500, 96, 64, 2.0)
     big = scenes.camera_relative_scene("b", 22, 20000, 320, 240, 6.0)
     rz._capacity_hint.clear()
+    rz.binning_stats(reset=True)
+    key_b = (torch.device(DEV), 320, 240)
     with torch.no_grad():
         _, cs, _, _ = helpers.run_cuda(small, small.views[0], DEV)   # no hint: NEED_BINNING -> resume
+        _, cb0, rb0, db0 = helpers.run_cuda(big, big.views[0], DEV)  # no hint for this image size either
+        rz._capacity_hint[key_b] = 100.0
         _, cb1, rb1, db1 = helpers.run_cuda(big, big.views[0], DEV)  # hint too small: speculative miss -> resume
         _, cb2, rb2, db2 = helpers.run_cuda(big, big.views[0], DEV)  # hint large enough: speculative hit
-        _, cs2, _, _ = helpers.run_cuda(small, small.views[0], DEV)  # oversized capacity
-    assert torch.equal(cb1, cb2) and torch.equal(db1, db2) and torch.equal(rb1, rb2)
+        _, cs2, _, _ = helpers.run_cuda(small, small.views[0], DEV)  # hit
+    assert torch.equal(cb1, cb2) and torch.equal(db1, db2) and torch.equal(rb1, rb2) and torch.equal(cb0, cb2)
     assert torch.equal(cs, cs2)
+    assert rz.binning_stats() == dict(calls=5, misses=1, sizing_calls=2)
+    # the hint is a high-water mark that decays by 1 % per call: a smaller view afterwards keeps the capacity
+    hwm = rz._capacity_hint[key_b]
+    sub = scenes.Scene("sub", big.means3D[:2000].contiguous(), big.scales[:2000].contiguous(), big.rotations[:2000].contiguous(),
+                       big.opacities[:2000].contiguous(), big.shs[:2000].contiguous(), big.bg, big.views)
+    with torch.no_grad():
+        helpers.run_cuda(sub, sub.views[0], DEV)
+        helpers.run_cuda(big, big.views[0], DEV)
+    assert abs(rz._capacity_hint[key_b] - hwm) <= 1e-6 * hwm and rz.binning_stats()["misses"] == 1
 
 
 @pytest.mark.parametrize("n,end_bit", [(1, 41), (255, 41), (3071, 45), (3072, 45), (3073, 47), (100_003, 44),

@@ -231,8 +231,10 @@ def test_deferred_sh_backward_and_accumulating_k9_against_oracle(split):
                    ("scales", buf.view("scales")), ("rotations", buf.view("rotations"))):
         e = helpers.rel_err(got, want[k].reshape(got.shape))
         assert e <= 1e-3, (k, e)
-        # element-wise, with a floor of 1 % of the largest entry: the sum over views cancels in some rows
-        assert helpers.elem_err(got, want[k].reshape(got.shape), floor_frac=1e-2) <= 0.05, k
+        # element-wise: no entry is off by more than 0.2 % of the largest one (the sum over views cancels in some rows,
+        # so an error relative to the entry itself is not meaningful there)
+        w = want[k].reshape(got.shape)
+        assert float((got.double().cpu() - w).abs().max()) <= 2e-3 * float(w.abs().max()), k
     assert helpers.rel_err(buf.view("densify_grad_accum"), accum_ref) <= 1e-3
     assert torch.equal(buf.view("densify_denom").cpu(), denom_ref)
 
