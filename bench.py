@@ -223,6 +223,21 @@ def stop_clock_sampler(proc, path):
     return out
 
 
+def _jsonable(o, path="line"):
+    """Plain python for json.dumps; a tensor / numpy scalar that slipped into the line is converted (and reported on
+    stderr with its key path, so that it gets fixed at the source)."""
+    if isinstance(o, dict):
+        return {str(k): _jsonable(v, f"{path}.{k}") for k, v in o.items()}
+    if isinstance(o, (list, tuple)):
+        return [_jsonable(v, f"{path}[{i}]") for i, v in enumerate(o)]
+    if torch.is_tensor(o):
+        print(f"bench.py: tensor at {path} converted for JSON", file=sys.stderr)
+        return o.item() if o.numel() == 1 else o.tolist()
+    if hasattr(o, "item") and not isinstance(o, (int, float, bool, str)):
+        return o.item()
+    return o
+
+
 def _pct(xs, q):
     xs = sorted(xs)
     return xs[min(len(xs) - 1, max(0, int(round(q * (len(xs) - 1)))))]
@@ -452,7 +467,7 @@ def main():
     barrier()
     clocks = stop_clock_sampler(sampler, sampler_path) if rank == 0 else None
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    binning = rz.binning_stats()              # warm-up + timed region of the batch path (this rank)
+    binning_stats = rz.binning_stats()        # warm-up + timed region of the batch path (this rank)
     checksum = grad_checksum(vp.buf)          # of the last timed step's all-reduced gradients (identical on all ranks)
     loss_sums_resident = [float(v) for v in vp.loss_acc.cpu()]
     # Per-stage durations (roofline / stages): a second measured region of the same steps with ONE view in flight.  In
@@ -506,11 +521,17 @@ def main():
     # ---------------- end-to-end with host buffers (`e2e`) ----------------
     e2e = None
     if not args.no_e2e:
-        d2h = 12  # the three loss sums
+        d2h = 12  # the three loss sums, read back every step
 
         staged = [None]
+        # The step's result (three loss sums) is read back EVERY step: an asynchronous device->host copy into pinned
+        # memory behind the step, consumed by the host one step later (after its event), so that the host keeps
+        # enqueueing the next step while the copy lands -- the loss.item() of a training loop that logs one step late.
+        loss_pinned = [torch.empty(3, dtype=torch.float32).pin_memory() for _ in range(2)]
+        loss_ready = [torch.cuda.Event(), torch.cuda.Event()]
+        loss_seen = []
 
-        def e2e_step(prefetch_next=True):
+        def e2e_step(k, prefetch_next=True):
             # this step's Gaussians: uploaded by the previous step's prefetch, or now (first step of a run)
             g = staged[0] if staged[0] is not None else vp.stage_gaussians(host)
             vs = [None] * n_views
@@ -523,10 +544,27 @@ def main():
             # (`steps` parameter uploads for `steps` steps)
             out = vp.step(g, vs, tg, prefetch_gaussians=host if prefetch_next else None)
             staged[0] = out["prefetched"]
-            return out["loss_sums"].cpu()  # device -> host read of the step's result (synchronises)
+            if os.environ.get("PDGS_E2E_SYNC_READBACK", "0") == "1":   # A/B switch: blocking read of this step's result
+                loss_seen.append(out["loss_sums"].cpu())
+                loss_ready[k & 1].record()
+                loss_pinned[k & 1].copy_(loss_seen[-1])
+                return
+            loss_pinned[k & 1].copy_(out["loss_sums"], non_blocking=True)
+            loss_ready[k & 1].record()
+            if k > 0:
+                loss_ready[(k - 1) & 1].synchronize()
+                loss_seen.append(loss_pinned[(k - 1) & 1].clone())
 
-        for _ in range(max(1, min(args.warmup, 2))):
-            e2e_step(prefetch_next=False)
+        def e2e_drain(k_last):
+            loss_ready[k_last & 1].synchronize()
+            if os.environ.get("PDGS_E2E_SYNC_READBACK", "0") != "1":
+                loss_seen.append(loss_pinned[k_last & 1].clone())
+            return loss_seen[-1]
+
+        nw = max(1, min(args.warmup, 2))
+        for k in range(nw):
+            e2e_step(k, prefetch_next=False)
+        e2e_drain(nw - 1)
         barrier()
         # N > 1: every rank uploaded 1/world of each tensor and an in-place all-gather over NVLink completed the
         # replicas; they must equal the host tensors bit for bit on every rank
@@ -545,10 +583,13 @@ def main():
         h2d0 = vp.h2d_bytes
         t0 = time.perf_counter()
         e0.record()
+        loss_seen.clear()
         for k in range(args.steps):
-            last = e2e_step(prefetch_next=(k + 1 < args.steps))
+            e2e_step(k, prefetch_next=(k + 1 < args.steps))
+        last = e2e_drain(args.steps - 1)   # every step's result has reached the host inside the timed region
         e1.record()
         barrier()
+        assert len(loss_seen) == args.steps
         wall = (time.perf_counter() - t0) * 1e3
         t = torch.tensor([max(wall, e0.elapsed_time(e1))], dtype=torch.float64, device=dev)
         # bytes actually copied host -> device per step by this rank: Gaussians (first step: the whole replica; later steps:
@@ -562,7 +603,9 @@ def main():
                    d2h_bytes_per_step=int(hb[1].item()), ms_per_step=float(t.item()) / args.steps,
                    api="pdgs_b200.viewparallel.ViewParallelRasterizer.step (C ABI: pdgs_forward / pdgs_image_loss / "
                        "pdgs_backward) fed from pinned host tensors; step k+1's Gaussians are uploaded during step k (each rank its "
-                       "1/world share over PCIe, replicas completed by an all-gather over NVLink), target images one view ahead",
+                       "1/world share over PCIe, replicas completed by an all-gather over NVLink), target images one view ahead; the "
+                       "loss sums of every step are copied device->host into pinned memory behind the step and read by the host "
+                       "one step later",
                    loss_mean=float(last[0].item()) / n_views, replicas_equal_host=replicas_ok,
                    grad_checksum=grad_checksum(vp.buf))
 
@@ -664,14 +707,14 @@ def main():
                 higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
                 config=workload_config(args, scene, world), clocks=clocks, e2e=e2e, gpu_launches=launches,
                 roofline=roofline, stages=stages, cpu_baseline=cpu_baseline, library_baselines=lib, dropin=dropin,
-                grad_checksum=checksum, loss_sums=loss_sums_resident, binning=binning,
+                grad_checksum=checksum, loss_sums=loss_sums_resident, binning=binning_stats,
                 stage_timing=dict(lanes=1, ms_per_step=ms_one_lane,
                                   note="stages / roofline come from a second measured region of the same steps with one view "
                                        "in flight; `value` is measured with config.lanes views in flight on separate streams"),
                 work_per_view=dict(P=Pn, visible=V, pairs=R, n_test=work["n_test"] / nv, n_acc=work["n_acc"] / nv,
                                    n_test_bwd=work["n_test_bwd"] / nv),
                 loss_mean=loss_mean)
-    print(json.dumps(line))
+    print(json.dumps(_jsonable(line)))
     if world > 1:
         dist.destroy_process_group()
     return 0
