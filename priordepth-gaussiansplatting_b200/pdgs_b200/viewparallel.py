@@ -184,8 +184,11 @@ class ViewParallelRasterizer:
         self._count_lock = threading.Lock()
         self._copy_stream = None
         self._color_grads = None
-        # chunks along P of the deferred SH backward when its rows are all-reduced behind it (world > 1); PDGS_REDUCE_CHUNKS
-        self.reduce_chunks = max(1, int(os.environ.get("PDGS_REDUCE_CHUNKS", "4")))
+        # chunks along P of the deferred SH backward when its rows are all-reduced behind it (world > 1); PDGS_REDUCE_CHUNKS.
+        # Measured on 8 x B200 (profiles/README.md r02h): 1 chunk 17.99 ms/step, 4 chunks 18.31 -- NCCL loses more on the
+        # smaller messages (732 MB in one call 1.80 ms, in 4 calls 2.07 ms) than the 0.5 ms SH kernel can hide, so the
+        # default is one chunk: only the 10 non-SH floats per Gaussian are reduced underneath the SH kernel.
+        self.reduce_chunks = max(1, int(os.environ.get("PDGS_REDUCE_CHUNKS", "1")))
 
     def _upload(self, i, targets, priors, masks, alphas=None):
         items = [targets[i], None if priors is None else priors.get(i), None if masks is None else masks.get(i),
