@@ -248,9 +248,9 @@ def dropin_row(args, scene, dev, iters=50, warmup=10, vary_r=False):
     loss `|clamp(render, 0, 1) - gt|.mean()` (torch ops, as /root/reference/gaussian_renderer/__init__.py:121 and
     train.py:153 do), one view per iteration cycling through the cameras, CUDA events, 10 warm-up + 50 timed,
     median / p10 / p90.  Honours CUDA_LAUNCH_BLOCKING from the environment (the reference sets it, train.py:65).
-    vary_r: every other camera is a 2x zoom of an orbit camera (about 3x the pairs) and the cameras are visited in a
-    seeded random order, as a training loop pops them (train.py:130-135), so the speculative binning capacity is
-    exercised with a pair count that jumps by more than 2x between calls; misses are counted."""
+    vary_r: every other camera renders with scale_modifier 2.5 (every splat 2.5x larger: about 3x the pairs) and the
+    cameras are visited in a seeded random order, as a training loop pops them (train.py:130-135), so the speculative
+    binning capacity is exercised with a pair count that jumps by more than 2x between calls; misses are counted."""
     import random
     from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
     from pdgs_b200 import rasterizer as rz
@@ -262,12 +262,9 @@ def dropin_row(args, scene, dev, iters=50, warmup=10, vary_r=False):
     rast, tgts = [], []
     for i in range(n):
         v = scene.views[i]
-        if vary_r and i % 2 == 1:   # same pose, half the field of view
-            w2c = v.world_view_transform.transpose(0, 1).double().numpy()
-            v = scenes.make_view(w2c, v.image_width, v.image_height, tanx=0.3125)
         rs = GaussianRasterizationSettings(
             image_height=v.image_height, image_width=v.image_width, tanfovx=v.tanfovx, tanfovy=v.tanfovy, bg=scene.bg.to(dev),
-            scale_modifier=1.0, viewmatrix=v.world_view_transform.to(dev), projmatrix=v.full_proj_transform.to(dev),
+            scale_modifier=2.5 if (vary_r and i % 2 == 1) else 1.0, viewmatrix=v.world_view_transform.to(dev), projmatrix=v.full_proj_transform.to(dev),
             sh_degree=scene.sh_degree, campos=v.camera_center.to(dev), prefiltered=False, debug=False, antialiasing=False)
         rast.append(GaussianRasterizer(raster_settings=rs))
         gen = torch.Generator().manual_seed(scenes.SEED0 + 1000 + i)
@@ -700,7 +697,16 @@ def main():
 
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
-        cpu_baseline, _ = cpu_arm(args, scene, 1, 2, 1)
+        # the SAME protocol and process conditions as the reference arm: run it as a child process (fresh interpreter, no
+        # CUDA context) on a bounded number of samples and take its cpu_baseline block
+        cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "6", "--warmup", "1", "--config",
+               args.config, "--views", str(args.views), "--scale-image", str(args.scale_image), "--cpu-window",
+               str(args.cpu_window[0]), str(args.cpu_window[1])] + (["--P", str(args.P)] if args.P else [])
+        try:
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+            cpu_baseline = json.loads([ln for ln in r.stdout.strip().splitlines() if ln.startswith("{")][-1])["cpu_baseline"]
+        except Exception as e:  # noqa: BLE001
+            cpu_baseline = dict(error=f"{type(e).__name__}: {e}"[:300])
 
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
                 ms_per_step=ms_total / args.steps, ms_per_view_per_gpu=ms_total / args.steps / max(len(my), 1),
