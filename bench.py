@@ -539,7 +539,8 @@ def main():
             # the NEXT step's Gaussians are uploaded by step() itself, slice by slice behind the image uploads, so the copy
             # overlaps this step's kernels; every step's host->device copy still happens inside the timed region
             # (`steps` parameter uploads for `steps` steps)
-            out = vp.step(g, vs, tg, prefetch_gaussians=host if prefetch_next else None)
+            out = vp.step(g, vs, tg, prefetch_gaussians=host if prefetch_next else None,
+                          prefetch_images=dict(targets=tg) if prefetch_next else None)
             staged[0] = out["prefetched"]
             if os.environ.get("PDGS_E2E_SYNC_READBACK", "0") == "1":   # A/B switch: blocking read of this step's result
                 loss_seen.append(out["loss_sums"].cpu())

@@ -184,6 +184,7 @@ class ViewParallelRasterizer:
         self._count_lock = threading.Lock()
         self._copy_stream = None
         self._color_grads = None
+        self._pre_images: Dict[int, tuple] = {}  # view index -> (host target tensor, staged upload) for the NEXT step
         # chunks along P of the deferred SH backward when its rows are all-reduced behind it (world > 1); PDGS_REDUCE_CHUNKS.
         # Measured on 8 x B200 (profiles/README.md r02h): 1 chunk 17.99 ms/step, 4 chunks 18.31 -- NCCL loses more on the
         # smaller messages (732 MB in one call 1.80 ms, in 4 calls 2.07 ms) than the 0.5 ms SH kernel can hide, so the
@@ -285,7 +286,7 @@ class ViewParallelRasterizer:
              priors: Optional[Dict[int, torch.Tensor]] = None, masks: Optional[Dict[int, torch.Tensor]] = None,
              w_depth: float = 0.0, reduce: bool = True, keep_outputs: bool = False, lambda_dssim: float = 0.0,
              prefetch_gaussians: Optional[Dict[str, torch.Tensor]] = None, clamp: bool = True,
-             alpha_masks: Optional[Dict[int, torch.Tensor]] = None) -> Dict:
+             alpha_masks: Optional[Dict[int, torch.Tensor]] = None, prefetch_images: Optional[Dict] = None) -> Dict:
         """gaussians: means3D/shs/opacities/scales/rotations (post-activation, as render() passes them,
         /root/reference/gaussian_renderer/__init__.py:57-112); optionally `shs_dc` + `shs_rest` instead of `shs`
         (features_dc / features_rest, gradients then in buf.view("shs_dc") / ("shs_rest")) and `raw_params=True`
@@ -301,7 +302,11 @@ class ViewParallelRasterizer:
         streams share one DMA queue, so a single 236 B/Gaussian copy issued up front would hold the images back and
         stall the kernels); with several ranks each rank uploads 1/world of every tensor and an all-gather over NVLink
         completes the replicas.  The handle comes back as out["prefetched"] and is passed as `gaussians` to the next
-        step.  Every rank must pass prefetch_gaussians in the same steps (it contains a collective)."""
+        step.  Every rank must pass prefetch_gaussians in the same steps (it contains a collective).
+
+        prefetch_images: dict(targets=..., priors=..., masks=..., alpha_masks=...) of the NEXT step (pinned host tensors).
+        Each lane uploads the images of the view it will start the next step with as soon as it has launched its last
+        view of this step, so the next step's first kernels do not wait for a 20 MB image to cross PCIe."""
         if isinstance(gaussians, tuple):  # handle from stage_gaussians(): wait for the upload on the compute stream
             gaussians, ev = gaussians
             if ev is not None:
@@ -336,7 +341,13 @@ class ViewParallelRasterizer:
             """The views `sub` = [(k, i), ...] of one lane, in order, on the calling thread's current stream."""
             res = []
             scratch = self._scratch.setdefault(lane, {})
-            pending = self._upload(sub[0][1], targets, priors, masks, alpha_masks) if sub else None
+            pending = None
+            if sub:
+                pre = self._pre_images.pop(sub[0][1], None)   # uploaded during the previous step?
+                if pre is not None and pre[0] is targets[sub[0][1]]:
+                    pending = pre[1]
+                else:
+                    pending = self._upload(sub[0][1], targets, priors, masks, alpha_masks)
             for n, (k, i) in enumerate(sub):
                 cur = pending
                 pending = self._upload(sub[n + 1][1], targets, priors, masks, alpha_masks) if n + 1 < len(sub) else None
@@ -352,6 +363,11 @@ class ViewParallelRasterizer:
                 else:
                     r = self.backend(gaussians, views[i], tgt, pri, msk, w_depth, acc_k, self.loss_acc)
                 res.append((k, r))
+            if prefetch_images is not None and sub:
+                i0, nt = sub[0][1], prefetch_images["targets"]
+                if i0 in nt:
+                    self._pre_images[i0] = (nt[i0], self._upload(i0, nt, prefetch_images.get("priors"),
+                                                                 prefetch_images.get("masks"), prefetch_images.get("alpha_masks")))
             return res
 
         if lanes == 1:

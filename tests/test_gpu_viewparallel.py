@@ -140,8 +140,11 @@ def test_step_from_staged_host_gaussians():
     b = ViewParallelRasterizer(sc.P, 16, DEV)
     handle = b.stage_gaussians(host)
     nxt = b.stage_gaussians(host)  # a second upload in flight, as the pipelined loop does
-    out = b.step(handle, views, tg_host, prefetch_gaussians=host)   # next step's parameters uploaded slice by slice
+    # next step's parameters uploaded slice by slice, and the first image(s) of the next step behind the last view
+    out = b.step(handle, views, tg_host, prefetch_gaussians=host, prefetch_images=dict(targets=tg_host))
+    assert len(b._pre_images) >= 1
     b.step(nxt, views, tg_host)
+    assert len(b._pre_images) == 0   # consumed by the step that followed
     b.step(out["prefetched"], views, tg_host)
     torch.cuda.synchronize()
     assert helpers.rel_err(b.buf.flat, a.buf.flat) < 1e-4
