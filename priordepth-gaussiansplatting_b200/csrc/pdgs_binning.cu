@@ -381,17 +381,23 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restr
 
 // Lanes of the warp holding the same digit.  Built from one ballot per digit bit: MATCH.ANY serialises over the
 // distinct values in the warp (about 100 cycles per instruction per SM with random 8-bit digits, ncu r01h) and
-// was the bottleneck of every pass.
-__device__ __forceinline__ unsigned warp_peers(uint32_t d, int nbits) {
+// was the bottleneck of every pass.  Four instructions per bit (predicate, VOTE, SELP, LOP3): the sort passes are bound
+// by the ALU pipe (ncu r02A: math-pipe throttle 1.6 stalls per issue, 170 instructions per key and pass), and the
+// round-1 form spent about six per bit plus a run-time test of the digit width.  The digit is already masked to its
+// width, so the bits above it are zero in every lane and their ballots change nothing: no width test is needed.
+__device__ __forceinline__ unsigned warp_peers(uint32_t d, int /*nbits*/) {
   unsigned peers = 0xffffffffu;
 #pragma unroll
   for (int b = 0; b < RADIX_BITS; ++b) {
-    if (b < nbits) {
-      const bool bit = (d & (1u << b)) != 0u;
-      const unsigned m = __ballot_sync(0xffffffffu, bit);
-      const unsigned x = bit ? 0xffffffffu : 0u;
-      peers &= ~(m ^ x);  // lanes whose bit b equals mine
-    }
+    unsigned m, x;
+    asm("{\n\t.reg .pred p;\n\t.reg .u32 t;\n\t"
+        "and.b32 t, %2, %3;\n\t"
+        "setp.ne.u32 p, t, 0;\n\t"
+        "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t"
+        "selp.u32 %1, 0xffffffff, 0, p;\n\t}"
+        : "=r"(m), "=r"(x)
+        : "r"(d), "r"(1u << b));
+    peers &= ~(m ^ x);  // lanes whose bit b equals mine
   }
   return peers;
 }

@@ -103,7 +103,11 @@ def _check_window(sc, view, st, win, color, invd, sv):
     assert torch.equal(nc[ok], res.n_contrib[ys, xs][ok])
     fT = sv["final_T"].view(H, W)[ys, xs].double().cpu()
     assert float((fT - res.final_T[ys, xs])[ok].abs().max()) <= 1e-5
-    print(f"  window {win}: {ids.numel()} Gaussians, {info['pairs_window']} pairs, fragile {float(frag.float().mean()):.2e}, "
+    # of the fragile pixels (a threshold within rounding distance in float64), how many did the fp32 kernel -- which forms
+    # alpha as ex2.approx(log2 o + log2e * power), not o * exp(power) -- actually decide the other way
+    flipped = int(((dc > IMG_TOL) & frag).sum())
+    print(f"  window {win}: {ids.numel()} Gaussians, {info['pairs_window']} pairs, fragile {float(frag.float().mean()):.2e} "
+          f"({int(frag.sum())} px, {flipped} of them differ by > 1e-4, worst {float(dc.max()):.1e}), "
           f"max|dC| {float(dc[ok].max()):.2e}, max|dD| {float(dd[ok].max()):.2e}")
     return o, ids, res
 
