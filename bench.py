@@ -500,6 +500,7 @@ def main():
     work = dict(P=P, V=0, R=0, n_test=0, n_acc=0, n_test_bwd=0, views=len(my), tiles=((W + 15) // 16) * ((H + 15) // 16),
                 HW=H * W)
     empty = torch.empty(0, device=dev)
+    rz.set_work_counters(dev, True)   # N_test / N_acc counters of the forward blend: only this untimed pass needs them
     with torch.no_grad():
         for i in my:
             rs = views_dev[i]
@@ -513,6 +514,7 @@ def main():
             work["n_test"] += c["n_tested"]
             work["n_acc"] += c["n_accepted"]
             work["n_test_bwd"] += c["n_contrib"]
+    rz.set_work_counters(dev, False)
     torch.cuda.synchronize(dev)
 
     # ---------------- end-to-end with host buffers (`e2e`) ----------------

@@ -144,6 +144,11 @@ enum {
   PDGS_STAGE_ADAM = 12, PDGS_STAGE_COUNT = 13
 };
 int pdgs_set_stage_timing(PdgsHandle* h, int32_t enable);
+/* Work counters (no reference counterpart): when enabled, the forward blend of this handle also writes, per pixel, the
+ * number of list entries a pixel-serial walk evaluates before the pixel stops (n_tested) and the number it blends
+ * (n_accepted) -- the N_test / N_acc of SURVEY 8(d)'s algorithmic FLOP count, read through pdgs_state_view.  Off by
+ * default: the counters cost instructions in the hottest loop and nothing of the path needs them. */
+int pdgs_set_work_counters(PdgsHandle* h, int32_t enable);
 int pdgs_stage_times(PdgsHandle* h, float* ms_sum, int32_t* counts, int32_t n);
 
 size_t pdgs_geom_bytes(int64_t P);
@@ -267,8 +272,8 @@ typedef struct PdgsStateView {
   const uint32_t* ranges;       /* [T,2] */
   const float* final_T;         /* [H*W] */
   const uint32_t* n_contrib;    /* [H*W] */
-  const uint32_t* n_tested;     /* [H*W] list entries evaluated by the forward blend */
-  const uint32_t* n_accepted;   /* [H*W] list entries blended */
+  const uint32_t* n_tested;     /* [H*W] list entries evaluated by the forward blend (valid with pdgs_set_work_counters) */
+  const uint32_t* n_accepted;   /* [H*W] list entries blended (valid with pdgs_set_work_counters) */
   const uint32_t* tiles_touched;/* [P] */
   const uint32_t* point_offsets;/* [P] inclusive scan of tiles_touched taken in depth order */
   const uint32_t* depth_order;  /* [P] Gaussian indices sorted by (depth bits, index); culled ones last */

@@ -25,6 +25,7 @@ struct PdgsHandle {
   double* dsums;                  // device double[8]: loss sums accumulated in double by the SSIM kernels
   cudaEvent_t ev;
   int timing;                     // per-stage events enabled
+  int work_counters;              // forward blend also writes n_tested / n_accepted
   std::vector<cudaEvent_t> pool;  // idle timing events
   std::vector<StageRec> recs;     // recorded since the last pdgs_stage_times()
 };
@@ -88,6 +89,7 @@ int pdgs_create(PdgsHandle** out) {
   PD_CUDA(cudaEventCreateWithFlags(&h->ev, cudaEventDisableTiming));
   PD_CUDA(cudaMalloc((void**)&h->dsums, 64));
   h->timing = 0;
+  h->work_counters = 0;
   *out = h;
   return PDGS_OK;
 }
@@ -108,6 +110,12 @@ int pdgs_set_stage_timing(PdgsHandle* h, int32_t enable) {
   h->timing = enable ? 1 : 0;
   for (StageRec& r : h->recs) { h->pool.push_back(r.b); h->pool.push_back(r.e); }
   h->recs.clear();
+  return PDGS_OK;
+}
+
+int pdgs_set_work_counters(PdgsHandle* h, int32_t enable) {
+  if (!h) return fail(PDGS_E_INVALID, "pdgs_set_work_counters: handle is NULL");
+  h->work_counters = enable ? 1 : 0;
   return PDGS_OK;
 }
 
@@ -220,7 +228,8 @@ static int run_binning_and_blend(PdgsHandle* h, const DeviceArgs& a, GeomView g,
   }
   {
     StageTimer t(h, PDGS_STAGE_BLEND_FWD, s);
-    PD_STEP(debug, s, launch_render_forward(a, g, im, b.point_list, b.pair_mask, st->capacity_pairs, out->color, out->invdepth, s));
+    PD_STEP(debug, s, launch_render_forward(a, g, im, b.point_list, b.pair_mask, st->capacity_pairs, out->color, out->invdepth,
+                                            h->work_counters, s));
   }
   return PDGS_OK;
 }

@@ -201,8 +201,10 @@ cudaError_t launch_sort_u64(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b
                             int64_t capacity, int npass, int end_bit, void* scratch, cudaStream_t s);
 cudaError_t launch_ranges(const uint32_t* tkeys, const uint32_t* n_dev, int64_t capacity, uint2* ranges, int tiles,
                           cudaStream_t s);
+// work_counters: also write ImageView::n_tested / n_accepted (roofline accounting; off on the product path)
 cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
-                                  uint8_t* pair_mask, int64_t capacity, float* out_color, float* out_invdepth, cudaStream_t s);
+                                  uint8_t* pair_mask, int64_t capacity, float* out_color, float* out_invdepth,
+                                  int work_counters, cudaStream_t s);
 cudaError_t launch_render_backward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
                                    uint8_t* pair_mask, const float* dL_dcolor, const float* dL_dinvdepth, float* acc, cudaStream_t s);
 struct GradPtrs {

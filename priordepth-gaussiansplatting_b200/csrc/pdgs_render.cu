@@ -194,6 +194,13 @@ __device__ __forceinline__ uint32_t highest_bit(uint32_t m) {
   asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(m));
   return r;
 }
+// mask of the hb low bits: and-ing it into the survivor mask clears its highest set bit hb in two instructions (BMSK +
+// LOP3) instead of the three of `rm ^= 1u << hb` (MOV 1, SHF, LOP3); the survivor loops are issue-bound
+__device__ __forceinline__ uint32_t low_bits(uint32_t hb) {
+  uint32_t r;
+  asm("bmsk.clamp.b32 %0, 0, %1;" : "=r"(r) : "r"(hb));
+  return r;
+}
 __device__ __forceinline__ uint32_t record_addr(uint32_t last_addr, uint32_t hb) {
   uint32_t r;
   asm("mad.lo.u32 %0, %1, 0xfffffff0, %2;" : "=r"(r) : "r"(hb), "r"(last_addr));
@@ -208,6 +215,10 @@ __device__ __forceinline__ float4 lds128_nv(uint32_t a) {  // not volatile: the 
 #ifndef PDGS_FWD_CTAS
 #define PDGS_FWD_CTAS 5
 #endif
+// COUNT: also produce the per-pixel work counters n_tested / n_accepted (roofline FLOP accounting of bench.py; enabled
+// per handle with pdgs_set_work_counters).  The product path runs COUNT = false: the counters cost two to three of the
+// ~42 instructions of the survivor loop.
+template <bool COUNT>
 __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const float4* __restrict__ gA, const float4* __restrict__ gB,
                                                             const float4* __restrict__ gC,
                                                             const uint2* __restrict__ ranges,
@@ -239,15 +250,17 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
     if (__all_sync(FULL, done)) continue;  // this warp's patch is finished; it only helps staging
     const int cnt = min((uint32_t)RT, range.y - base);
     const uint32_t pos0 = base - range.x;
+    // shared address of the record of the last entry blended / of the entry that ended the pixel in THIS batch (0 = none):
+    // one move inside the loop, the list position is formed from it once per batch
+    uint32_t hit_rec = 0, end_rec = 0;
     for (int k = 0; k * 32 < cnt; ++k) {
       // survivors of this warp's patch, bit-reversed so that the leading one is the first list entry
       uint32_t rm = __brev(__ballot_sync(FULL, (st.mask[k * 32 + lane] & wbit) != 0));
       const uint32_t last_rec = st_addr + 16u * (uint32_t)(k * 32 + 31);
       while (rm) {
         const uint32_t hb = highest_bit(rm);
-        rm ^= 1u << hb;
-        const uint32_t rec = record_addr(last_rec, hb);
-        const int j = k * 32 + 31 - (int)hb;
+        rm &= low_bits(hb);
+        const uint32_t rec = record_addr(last_rec, hb);  // entry j = k*32 + 31 - hb
         const float4 a = lds128_nv(rec);
         const float4 b = lds128_nv(rec + FWD_ST_B);
         const float dx = a.x - pxf, dy = a.y - pyf;
@@ -257,7 +270,7 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
         const float test_T = T * (1.0f - alpha);
         if (test_T < T_EPS) {
           done = true;
-          tested = pos0 + j + 1;
+          if (COUNT) end_rec = rec;
           continue;
         }
         float2 c;
@@ -268,18 +281,22 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
         C2 = fmaf(c.y, w, C2);
         D = fmaf(b.z, w, D);
         T = test_T;
-        last = pos0 + j + 1;
-        ++accepted;
+        hit_rec = rec;
+        if (COUNT) ++accepted;
       }
       if (__all_sync(FULL, done)) break;
     }
+    if (hit_rec) last = pos0 + ((hit_rec - st_addr) >> 4) + 1u;
+    if (COUNT && end_rec) tested = pos0 + ((end_rec - st_addr) >> 4) + 1u;
   }
   if (inside) {
     const size_t pix = (size_t)py * W + px, hw = (size_t)W * H;
     final_T[pix] = T;
     n_contrib[pix] = last;
-    n_tested[pix] = tested;      // list entries a pixel-serial walk evaluates before this pixel stops
-    n_accepted[pix] = accepted;
+    if (COUNT) {
+      n_tested[pix] = tested;      // list entries a pixel-serial walk evaluates before this pixel stops
+      n_accepted[pix] = accepted;
+    }
     out_color[pix] = C0 + T * __ldg(bg + 0);
     out_color[hw + pix] = C1 + T * __ldg(bg + 1);
     out_color[2 * hw + pix] = C2 + T * __ldg(bg + 2);
@@ -321,6 +338,14 @@ __device__ __forceinline__ void sts32(uint32_t a, uint32_t x) { asm volatile("st
 
 #ifndef PDGS_BWD_FB
 #define PDGS_BWD_FB 8
+#endif
+// measured (profiles/README.md r02B, C4, blend_bwd ms): rm ^= 1 << hb 0.834, BMSK form 0.826; panel-full test on the
+// row pointer instead of a slot counter 0.856 (one instruction less per survivor, yet slower), so the counter stays
+#ifndef PDGS_BWD_BMSK
+#define PDGS_BWD_BMSK 1
+#endif
+#ifndef PDGS_BWD_SLOTPTR
+#define PDGS_BWD_SLOTPTR 0
 #endif
 #ifndef PDGS_BWD_CTAS
 #define PDGS_BWD_CTAS 4
@@ -461,7 +486,9 @@ __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(cons
   // the next is T and ONE scalar `behind` (four FMAs per pair instead of the per-channel accum_rec updates).
   float T = T_final;
   float behind = -T_final * (__ldg(bg + 0) * gp0 + __ldg(bg + 1) * gp1 + __ldg(bg + 2) * gp2);
+#if !PDGS_BWD_SLOTPTR
   int slot = 0;
+#endif
   uint32_t wrow = wp;  // shared address of the panel row being filled
 
   for (uint32_t done = 0; done < todo; done += RT) {
@@ -484,7 +511,11 @@ __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(cons
       const uint32_t pos_last = top - (uint32_t)(k * 32 + 31);  // list position of the block's last entry (may wrap: only used + hb)
       while (rm) {
         const uint32_t hb = highest_bit(rm);  // entry j = k*32 + 31 - hb
+#if PDGS_BWD_BMSK
+        rm &= low_bits(hb);
+#else
         rm ^= 1u << hb;
+#endif
         const uint32_t rec = record_addr(last_rec, hb);
         const float4 a = lds128(rec), b = lds128(rec + ST_B);
         const float dx = a.x - pxf, dy = a.y - pyf;
@@ -513,27 +544,45 @@ __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(cons
           sts64(wrow + PR_GXY, a.x, a.y);  // every lane stores the same words: no lane predicate, no conflict
           sts32(wrow + PR_POS, row_id);
           wrow += PROW;
+#if PDGS_BWD_SLOTPTR
+          if (wrow == wp + FB * PROW) {  // panel full
+            flush_panel(wp, FB, lane, X0f, Y0f, acc);
+            wrow = wp;
+          }
+#else
           if (++slot == FB) {
             flush_panel(wp, FB, lane, X0f, Y0f, acc);
             slot = 0;
             wrow = wp;
           }
+#endif
         }
       }
     }
   }
+#if PDGS_BWD_SLOTPTR
+  if (wrow != wp) flush_panel(wp, (int)((wrow - wp) / PROW), lane, X0f, Y0f, acc);
+#else
   if (slot > 0) flush_panel(wp, slot, lane, X0f, Y0f, acc);
+#endif
 }
 
 }  // namespace
 
 cudaError_t launch_render_forward(const DeviceArgs& a, GeomView g, ImageView im, const uint32_t* point_list,
-                                  uint8_t* pair_mask, int64_t capacity, float* out_color, float* out_invdepth, cudaStream_t s) {
+                                  uint8_t* pair_mask, int64_t capacity, float* out_color, float* out_invdepth,
+                                  int work_counters, cudaStream_t s) {
   (void)capacity;
   if (a.W <= 0 || a.H <= 0) return cudaSuccess;
   dim3 grid(a.grid_x, a.grid_y);
-  render_forward_kernel<<<grid, RT, 0, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, pair_mask, a.W, a.H, a.bg, out_color,
-                                            out_invdepth, im.final_T, im.n_contrib, im.n_tested, im.n_accepted);
+  if (work_counters)
+    render_forward_kernel<true><<<grid, RT, 0, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, pair_mask, a.W, a.H, a.bg,
+                                                    out_color, out_invdepth, im.final_T, im.n_contrib, im.n_tested,
+                                                    im.n_accepted);
+  else
+    render_forward_kernel<false><<<grid, RT, 0, s>>>(g.gA, g.gB, g.gC, im.ranges, point_list, pair_mask, a.W, a.H, a.bg,
+                                                     out_color, out_invdepth, im.final_T, im.n_contrib, im.n_tested,
+                                                     im.n_accepted);
   return cudaGetLastError();
 }
 

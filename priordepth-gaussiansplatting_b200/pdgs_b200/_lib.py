@@ -68,6 +68,7 @@ SYMBOLS = {
     "pdgs_create": (C.c_int, [C.POINTER(vp)]),
     "pdgs_destroy": (C.c_int, [vp]),
     "pdgs_set_stage_timing": (C.c_int, [vp, C.c_int32]),
+    "pdgs_set_work_counters": (C.c_int, [vp, C.c_int32]),
     "pdgs_stage_times": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_int32]),
     "pdgs_image_loss": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, vp, vp,
                                   vp, vp]),

@@ -581,6 +581,15 @@ def set_stage_timing(device, enable: bool) -> None:
             L.check(L.lib().pdgs_set_stage_timing(h, int(bool(enable))), "pdgs_set_stage_timing")
 
 
+def set_work_counters(device, enable: bool) -> None:
+    """Turn the forward blend's per-pixel work counters (n_tested / n_accepted, read by image_counters / state_view) on
+    or off for the CALLING thread's handle on `device`.  They are off by default (C ABI pdgs_set_work_counters)."""
+    dev = torch.device(device)
+    with torch.cuda.device(dev):
+        idx = dev.index if dev.index is not None else torch.cuda.current_device()
+        L.check(L.lib().pdgs_set_work_counters(L.handle(idx), int(bool(enable))), "pdgs_set_work_counters")
+
+
 def stage_times(device) -> dict:
     """{stage: (summed duration in ms, number of launches of the stage)} since the previous call on `device`,
     summed over the handles of all threads (waits for the recorded work)."""
