@@ -316,6 +316,31 @@ def test_onesweep_sort_matches_stable_sort(n, end_bit):
     np.testing.assert_array_equal(ko.cpu().numpy(), keys.numpy()[order])
 
 
+def test_work_counters_match_the_oracle_counts():
+    """pdgs_set_work_counters: N_test / N_acc of SURVEY 8(d)'s FLOP count, as bench.py's roofline uses them, against the
+    oracle's exact counts (off by default; the forward runs its counter-free variant otherwise)."""
+    from pdgs_b200 import rasterizer as rz
+    sc = scenes.make_config("C1")
+    view = sc.views[0]
+    o, res, st = helpers.run_oracle(sc, view, need_grad=False)
+    rz.set_work_counters(DEV, True)
+    try:
+        with torch.no_grad():
+            rs = helpers.cuda_settings(sc, view, DEV)
+            empty = torch.empty(0, device=DEV)
+            g = {k: getattr(sc, k).to(DEV) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+            R, color, radii, geom, binning, img, invd = rz.rasterize_gaussians(
+                rs.bg, g["means3D"], empty, g["opacities"], g["scales"], g["rotations"], 1.0, empty, rs.viewmatrix,
+                rs.projmatrix, rs.tanfovx, rs.tanfovy, view.image_height, view.image_width, g["shs"], 3, rs.campos, False,
+                False, False)
+            c = rz.image_counters(geom, binning, img, sc.P, view.image_width, view.image_height)
+    finally:
+        rz.set_work_counters(DEV, False)
+    assert abs(c["n_accepted"] - res.n_acc) <= 2e-3 * res.n_acc
+    assert abs(c["n_tested"] - res.n_test) <= 2e-3 * res.n_test
+    assert abs(c["n_contrib"] - res.n_test_bwd) <= 2e-3 * res.n_test_bwd
+
+
 def test_mark_visible():
     from diff_gaussian_rasterization import GaussianRasterizer
     sc = scenes.make_config("C4", P=5000, n_views=3, scale_image=0.1)
