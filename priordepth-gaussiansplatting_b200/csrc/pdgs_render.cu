@@ -215,6 +215,9 @@ __device__ __forceinline__ float4 lds128_nv(uint32_t a) {  // not volatile: the 
 #ifndef PDGS_FWD_CTAS
 #define PDGS_FWD_CTAS 5
 #endif
+#ifndef PDGS_FWD_NOBRANCH
+#define PDGS_FWD_NOBRANCH 1
+#endif
 // COUNT: also produce the per-pixel work counters n_tested / n_accepted (roofline FLOP accounting of bench.py; enabled
 // per handle with pdgs_set_work_counters).  The product path runs COUNT = false: the counters cost two to three of the
 // ~42 instructions of the survivor loop.
@@ -266,6 +269,27 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
         const float dx = a.x - pxf, dy = a.y - pyf;
         const float t = gauss_exponent(dx, dy, a.z, a.w, b.x, b.y);
         const float alpha = fminf(ALPHA_MAX, ex2_approx(t));
+#if PDGS_FWD_NOBRANCH
+        // no divergent branch: every lane evaluates the blend, the updates are selects
+        const bool skip = done || t > b.y || alpha < ALPHA_MIN;
+        const float test_T = T * (1.0f - alpha);
+        const bool ends = !skip && test_T < T_EPS;
+        const bool ok = !skip && !ends;
+        float2 c;
+        asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(c.x), "=f"(c.y) : "r"(rec + FWD_ST_C));
+        const float w = alpha * T;
+        C0 = ok ? fmaf(b.w, w, C0) : C0;
+        C1 = ok ? fmaf(c.x, w, C1) : C1;
+        C2 = ok ? fmaf(c.y, w, C2) : C2;
+        D = ok ? fmaf(b.z, w, D) : D;
+        T = ok ? test_T : T;
+        hit_rec = ok ? rec : hit_rec;
+        done = done || ends;
+        if (COUNT) {
+          if (ends) end_rec = rec;
+          if (ok) ++accepted;
+        }
+#else
         if (done || t > b.y || alpha < ALPHA_MIN) continue;
         const float test_T = T * (1.0f - alpha);
         if (test_T < T_EPS) {
@@ -283,6 +307,7 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
         T = test_T;
         hit_rec = rec;
         if (COUNT) ++accepted;
+#endif
       }
       if (__all_sync(FULL, done)) break;
     }
@@ -346,6 +371,14 @@ __device__ __forceinline__ void sts32(uint32_t a, uint32_t x) { asm volatile("st
 #endif
 #ifndef PDGS_BWD_SLOTPTR
 #define PDGS_BWD_SLOTPTR 0
+#endif
+// r02C (same probe): per-pixel block without a divergent branch 0.826 -> 0.809; list-position test as one signed
+// compare against a per-32-block limit 0.826 -> 0.820; both 0.803
+#ifndef PDGS_BWD_NOBRANCH
+#define PDGS_BWD_NOBRANCH 1
+#endif
+#ifndef PDGS_BWD_THR
+#define PDGS_BWD_THR 1
 #endif
 #ifndef PDGS_BWD_CTAS
 #define PDGS_BWD_CTAS 4
@@ -509,6 +542,10 @@ __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(cons
       uint32_t rm = __brev(mw);  // leading one = first entry to visit
       const uint32_t last_rec = sst + 16u * (uint32_t)(k * 32 + 31);
       const uint32_t pos_last = top - (uint32_t)(k * 32 + 31);  // list position of the block's last entry (may wrap: only used + hb)
+#if PDGS_BWD_THR
+      // pos = pos_last + hb < last_contributor  <=>  (int)hb < (int)(last_contributor - pos_last): one compare per survivor
+      const int hb_limit = (int)(last_contributor - pos_last);
+#endif
       while (rm) {
         const uint32_t hb = highest_bit(rm);  // entry j = k*32 + 31 - hb
 #if PDGS_BWD_BMSK
@@ -522,12 +559,33 @@ __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(cons
         const float t = gauss_exponent(dx, dy, a.z, a.w, b.x, b.y);
         const float araw = ex2_approx(t);  // o * G
         const float alpha = fminf(ALPHA_MAX, araw);
+#if PDGS_BWD_THR
+        const bool active = ((int)hb < hb_limit) && !(t > b.y) && !(alpha < ALPHA_MIN);
+#else
         const uint32_t pos = pos_last + hb;  // = top - j
         const bool active = (pos < last_contributor) && !(t > b.y) && !(alpha < ALPHA_MIN);
+#endif
         if (__any_sync(FULL, active)) {
           float z = 0.f, w = 0.f;
           const float4 c = lds128(rec + ST_C);  // uniform address: one broadcast wavefront
           const uint32_t row_id = __float_as_uint(c.z);
+#if PDGS_BWD_NOBRANCH
+          {  // no divergent branch: every lane evaluates, inactive lanes keep their state and store zeros
+            const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
+            const float Tn = T * inv;
+            const float wv = alpha * Tn;
+            float q = b.w * gp0;
+            q = fmaf(c.x, gp1, q);
+            q = fmaf(c.y, gp2, q);
+            q = fmaf(b.z, gpd, q);
+            const float dL_dalpha = fmaf(Tn, q, behind * inv);
+            const float bn = fmaf(-wv, q, behind);
+            T = active ? Tn : T;
+            behind = active ? bn : behind;
+            w = active ? wv : 0.f;
+            z = active ? araw * dL_dalpha : 0.f;
+          }
+#else
           if (active) {
             const float inv = rcp_approx(1.0f - alpha);  // 1 - alpha >= 0.01
             T *= inv;
@@ -540,6 +598,7 @@ __global__ void __launch_bounds__(RT, PDGS_BWD_CTAS) render_backward_kernel(cons
             behind = fmaf(-w, q, behind);
             z = araw * dL_dalpha;  // = o * G * dL/dalpha; K8/K9 takes the factor o into account
           }
+#endif
           sts64(wrow + 8 * lane, z, w);
           sts64(wrow + PR_GXY, a.x, a.y);  // every lane stores the same words: no lane predicate, no conflict
           sts32(wrow + PR_POS, row_id);
