@@ -440,12 +440,18 @@ __global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? (ITEMS <= 
   KeyT key[ITEMS];
   uint32_t rank[ITEMS];
   const int seg = warp * ITEMS * 32;
+  const bool full = valid == TILE_ITEMS;  // every tile but the last: no per-item bounds test (the passes are ALU-bound)
+  if (full) {
 #pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const int local = seg + i * 32 + lane;
-    key[i] = (local < valid) ? keys_in[tile_base + local]
-                             : (KeyT)~(KeyT)0;  // padding: digit = digit_mask, the last bin in use; ranked behind every real key of that
-                                                // bin (higher local index), so it lands in slots >= valid and is dropped
+    for (int i = 0; i < ITEMS; ++i) key[i] = keys_in[tile_base + seg + i * 32 + lane];
+  } else {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int local = seg + i * 32 + lane;
+      key[i] = (local < valid) ? keys_in[tile_base + local]
+                               : (KeyT)~(KeyT)0;  // padding: digit = digit_mask, the last bin in use; ranked behind every real key of that
+                                                  // bin (higher local index), so it lands in slots >= valid and is dropped
+    }
   }
   // per-warp stable ranking: peers of every item first (independent MATCH ops), then one shared-memory atomic
   // per (item, distinct digit) issued back to back -- program order keeps equal digits of later items behind
@@ -526,10 +532,15 @@ __global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? (ITEMS <= 
     rank[i] = slot;
   }
   uint32_t val[ITEMS];
+  if (full && vals_in) {
 #pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const int local = seg + i * 32 + lane;
-    val[i] = (local < valid) ? (vals_in ? vals_in[tile_base + local] : (uint32_t)(tile_base + local)) : 0u;
+    for (int i = 0; i < ITEMS; ++i) val[i] = vals_in[tile_base + seg + i * 32 + lane];
+  } else {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int local = seg + i * 32 + lane;
+      val[i] = (local < valid) ? (vals_in ? vals_in[tile_base + local] : (uint32_t)(tile_base + local)) : 0u;
+    }
   }
   // Decoupled look-back for digit d, LB_WIDTH predecessors per round trip.  All resident CTAs publish their aggregates
   // at about the same time, so a tile walks back over ~30 of them on average before it meets an inclusive prefix (ncu
