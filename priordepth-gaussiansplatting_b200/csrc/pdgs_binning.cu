@@ -678,8 +678,11 @@ static cudaError_t sort_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint3
   uint32_t* vin = (npass % 2 == 0) ? vals_a : vals_b;
   KeyT* kout = (npass % 2 == 0) ? keys_b : keys_a;
   uint32_t* vout = (npass % 2 == 0) ? vals_b : vals_a;
+  // every block ends with npass * 256 global atomics on the same 256-entry histograms, so the block count, not the key
+  // count, sets the cost of small inputs: PDGS_HIST_CTAS_PER_SM blocks per SM at most
+  static const int hist_per_sm = [] { const char* e = getenv("PDGS_HIST_CTAS_PER_SM"); return e ? atoi(e) : 4; }();
   int hist_blocks = (int)((capacity + 256 * 16 - 1) / (256 * 16));
-  if (hist_blocks > 148 * 8) hist_blocks = 148 * 8;
+  if (hist_blocks > 148 * hist_per_sm) hist_blocks = 148 * hist_per_sm;
   if (hist_blocks < 1) hist_blocks = 1;
   sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(kin, n_dev, n_host, capacity, npass, end_bit, sc.hist);
   e = cudaGetLastError();
