@@ -549,12 +549,14 @@ __global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? (ITEMS <= 
   // word that is still empty.
   uint32_t excl = 0;
   if (tile > 0) {
-    int64_t t = (int64_t)tile - 1;
+    // 32-bit tile arithmetic (ntiles < 2^22) and one base pointer per thread: the loop is instruction- and latency-bound
+    const uint32_t* lb_d = lookback + d;
+    int t = (int)tile - 1;
     bool found = false;
     while (!found) {
       uint32_t w[LB_WIDTH];
 #pragma unroll
-      for (int j = 0; j < LB_WIDTH; ++j) w[j] = (t - j >= 0) ? ld_relaxed_u32(lookback + (size_t)(t - j) * RADIX + d) : LB_INC;
+      for (int j = 0; j < LB_WIDTH; ++j) w[j] = (t >= j) ? ld_relaxed_u32(lb_d + (size_t)(uint32_t)(t - j) * RADIX) : LB_INC;
       uint32_t lowest = w[0];
 #pragma unroll
       for (int j = 1; j < LB_WIDTH; ++j) lowest = min(lowest, w[j]);
@@ -563,7 +565,7 @@ __global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? (ITEMS <= 
         for (int j = 0; j < LB_WIDTH; ++j) {
           if (!found) {
             uint32_t v = w[j];
-            while ((v >> 30) == 0u) v = ld_relaxed_u32(lookback + (size_t)(t - j) * RADIX + d);
+            while ((v >> 30) == 0u) v = ld_relaxed_u32(lb_d + (size_t)(uint32_t)(t - j) * RADIX);
             excl += v & LB_MASK;
             found = (v >> 30) == 2u;
           }
