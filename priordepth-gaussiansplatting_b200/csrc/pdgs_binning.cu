@@ -147,7 +147,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(GeomView g, int64_t 
 // with a binary search over the segment's offsets in shared memory.  Every store is fully coalesced and
 // a rect of thousands of tiles costs the same per pair as a rect of one.
 // ------------------------------------------------------------------------------------------
-constexpr int DUP_SEG = 128;  // sorted Gaussians per warp
+constexpr int DUP_SEG = PDGS_DUP_SEG;  // sorted Gaussians per warp
+constexpr int DUP_SEARCH = DUP_SEG <= 64 ? 6 : (DUP_SEG <= 128 ? 7 : 8);  // binary-search steps over a segment's offsets
+static_assert(DUP_SEG == 64 || DUP_SEG == 128 || DUP_SEG == 256, "segment size");
 constexpr int DUP_WARPS = 8;
 
 __global__ void __launch_bounds__(DUP_WARPS * 32) duplicate_kernel(GeomView g, int64_t P, int grid_x,
@@ -181,7 +183,7 @@ __global__ void __launch_bounds__(DUP_WARPS * 32) duplicate_kernel(GeomView g, i
     // largest j in [0, n) with off[j] <= pos  (off is non-decreasing; empty Gaussians have off[j] == off[j+1])
     int lo = 0, hi = n;  // invariant: off[lo] <= pos < off[hi]
 #pragma unroll
-    for (int it = 0; it < 7; ++it) {
+    for (int it = 0; it < DUP_SEARCH; ++it) {
       const int mid = (lo + hi) >> 1;
       if (hi - lo > 1) {
         if (off[mid] <= pos) lo = mid; else hi = mid;
@@ -300,7 +302,7 @@ __global__ void __launch_bounds__(DUP_WARPS * 32) scan_duplicate_kernel(GeomView
     // largest j in [0, n) with off[j] <= e  (off is non-decreasing; empty Gaussians have off[j] == off[j+1])
     int lo = 0, hi = n;  // invariant: off[lo] <= e < off[hi]
 #pragma unroll
-    for (int it = 0; it < 7; ++it) {
+    for (int it = 0; it < DUP_SEARCH; ++it) {
       const int mid = (lo + hi) >> 1;
       if (hi - lo > 1) {
         if (off[mid] <= e) lo = mid; else hi = mid;

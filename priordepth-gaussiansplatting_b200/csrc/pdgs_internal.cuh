@@ -24,7 +24,10 @@ constexpr int DEPTH_SORT_PASSES = 4;
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 16;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;  // 4096 counts per CTA
-constexpr int DUP_TILE = 1024;  // sorted Gaussians per CTA of the fused scan + duplicate kernel (8 warps x 128)
+#ifndef PDGS_DUP_SEG
+#define PDGS_DUP_SEG 128
+#endif
+constexpr int DUP_TILE = 8 * PDGS_DUP_SEG;  // sorted Gaussians per CTA of the fused scan + duplicate kernel (8 warps x DUP_SEG)
 constexpr uint32_t MAX_PAIRS = 1u << 30;               // look-back words carry 30-bit counts
 
 // Control block at the start of the geometry blob (device memory, 256 B).
