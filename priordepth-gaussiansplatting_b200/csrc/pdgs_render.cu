@@ -213,7 +213,7 @@ __device__ __forceinline__ float4 lds128_nv(uint32_t a) {  // not volatile: the 
 }
 
 #ifndef PDGS_FWD_CTAS
-#define PDGS_FWD_CTAS 5
+#define PDGS_FWD_CTAS 4
 #endif
 #ifndef PDGS_FWD_NOBRANCH
 #define PDGS_FWD_NOBRANCH 1
@@ -381,7 +381,7 @@ __device__ __forceinline__ void sts32(uint32_t a, uint32_t x) { asm volatile("st
 #define PDGS_BWD_THR 1
 #endif
 #ifndef PDGS_BWD_CTAS
-#define PDGS_BWD_CTAS 4
+#define PDGS_BWD_CTAS 5
 #endif
 constexpr int FB = PDGS_BWD_FB;   // Gaussians per phase-2 panel (8 or 16)
 constexpr int FPARTS = 32 / FB;   // lanes per panel row in phase 2; each covers FB pixels = FB/8 pixel rows of the patch

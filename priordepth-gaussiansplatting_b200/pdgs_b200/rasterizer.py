@@ -24,15 +24,22 @@ from . import _lib as L
 _capacity_hint = {}
 _CAP_HEADROOM, _CAP_DECAY = 1.25, 0.99
 _binning_stats = {"calls": 0, "misses": 0, "sizing_calls": 0}
+_binning_lock = threading.Lock()   # the view-parallel lanes call in from several host threads
+
+
+def _count(key: str) -> None:
+    with _binning_lock:
+        _binning_stats[key] += 1
 
 
 def binning_stats(reset: bool = False) -> dict:
     """{"calls", "misses", "sizing_calls"}: forwards run, forwards whose speculative binning capacity was too small
     (duplicate + sort + blend ran twice), forwards that had no capacity hint yet (scan only, then the real pass)."""
-    out = dict(_binning_stats)
-    if reset:
-        for k in _binning_stats:
-            _binning_stats[k] = 0
+    with _binning_lock:
+        out = dict(_binning_stats)
+        if reset:
+            for k in _binning_stats:
+                _binning_stats[k] = 0
     return out
 
 
@@ -186,9 +193,9 @@ def rasterize_gaussians(bg, means3D, colors_precomp, opacities, scales, rotation
         per_bin = 1 + 2 + _passes(tiles) + 1 + 1           # scan + duplicate, 2 histograms, radix passes (4 depth + tile id), ranges, blend
         if cap > 0:
             launches += per_bin
-        _binning_stats["calls"] += 1
+        _count("calls")
         if rc == L.PDGS_NEED_BINNING:
-            _binning_stats["misses" if cap > 0 else "sizing_calls"] += 1
+            _count("misses" if cap > 0 else "sizing_calls")
             cap = max(int(R.value * _CAP_HEADROOM) + 4096, 4096)
             binning = torch.empty(lib.pdgs_binning_bytes(cap, P), **u8)
             st = _state(geom, image, binning, cap)
