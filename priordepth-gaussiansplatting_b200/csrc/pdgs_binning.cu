@@ -323,6 +323,9 @@ __global__ void __launch_bounds__(DUP_WARPS * 32) scan_duplicate_kernel(GeomView
 // Keys are u32 (depth bits / tile ids) inside the rasterizer; the u64 instantiation serves the
 // stand-alone pdgs_sort_pairs entry point.
 // ------------------------------------------------------------------------------------------
+#ifndef PDGS_SORT_CTAS
+#define PDGS_SORT_CTAS 4  // resident CTAs per SM of the u32 onesweep pass (64 registers)
+#endif
 #ifndef PDGS_LB_WIDTH
 #define PDGS_LB_WIDTH 4
 #endif
@@ -409,7 +412,7 @@ __device__ __forceinline__ unsigned warp_peers(uint32_t d, int /*nbits*/) {
 }
 
 template <typename KeyT, int ITEMS>
-__global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? (ITEMS <= 8 ? 6 : 4) : 3) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
+__global__ void __launch_bounds__(SORT_THREADS, (sizeof(KeyT) == 4) ? (ITEMS <= 8 ? 6 : PDGS_SORT_CTAS) : 3) sort_onesweep_kernel(const KeyT* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     KeyT* __restrict__ keys_out,
                                                                     uint32_t* __restrict__ vals_out, const uint32_t* n_dev,
