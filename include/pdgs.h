@@ -263,6 +263,25 @@ size_t pdgs_sort_scratch_bytes(int64_t n);
 int pdgs_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int64_t n,
                     int32_t end_bit, void* scratch, size_t scratch_bytes, void* stream);
 
+/* The same sort for callers that are not allowed to allocate device memory.  No counterpart in the reference:
+ * upstream sizes CUB's temporary storage through its resize callbacks and lets torch allocate it.  Typical users are
+ * hosts where all device memory belongs to somebody else -- an engine or inference server whose memory manager took
+ * the whole budget at start-up, a plugin invoked inside another program's frame loop where a cudaMalloc would
+ * stall every stream on the device, or an embedded deployment with a fixed memory map.
+ *
+ * The working memory is a fixed array inside libpdgs.so (about 2.7 MiB of device memory on every GPU the library is
+ * loaded on, held until the process exits), large enough for PDGS_SORT_STATIC_MAX_PAIRS pairs; larger n is refused
+ * with PDGS_E_INVALID and a message naming the limit.  The call allocates nothing, on host or device, and neither
+ * does anything it calls.  Output is identical to pdgs_sort_pairs; keys_in / vals_in are clobbered the same way.
+ *
+ * Set-up: the first call on each device (made with that device current) looks up the array's device address; do that
+ * first call before beginning a stream capture.  Sharing: every call on a device uses the same array.  Each sort
+ * clears what it needs on entry, so nothing has to be reset between calls, but two calls whose GPU work overlaps
+ * (different streams or host threads) race on it -- serialise them on one stream or with events. */
+#define PDGS_SORT_STATIC_MAX_PAIRS (1 << 20)
+int pdgs_sort_pairs_static(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int64_t n,
+                           int32_t end_bit, void* stream);
+
 /* Read-only views into the saved state, for parity tests (device pointers, valid until the
  * state buffers are freed). */
 typedef struct PdgsStateView {

@@ -10,6 +10,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
 #include <vector>
 
 #include "../../include/pdgs.h"
@@ -64,6 +65,45 @@ static int fail(int code, const char* fmt, const char* detail = "") {
       return PDGS_E_CUDA;                                                    \
     }                                                                        \
   } while (0)
+
+// ---- scratch for pdgs_sort_pairs_static ------------------------------------------------------------------------------
+// Some hosts of this library may not allocate device memory while they run: a renderer embedded in an engine whose
+// memory manager owns the whole device budget, a plugin called from inside somebody else's frame loop where a
+// cudaMalloc (a device-wide synchronisation) would stall every other stream, or a process that handed all of its
+// memory to a pool up front and has nothing left to ask the driver for.  For them the sort's working memory lives
+// in the library image itself: one fixed array per GPU, resident from the moment the library is loaded on that GPU
+// until the process exits, whether or not the entry point is ever called.
+//
+// The size follows carve_sort_scratch() for STATIC_SORT_MAX_PAIRS pairs in tiles of SORT_THREADS * SORT_ITEMS_U64:
+// 8 digit histograms, 8 tickets, 8 passes of per-tile look-back words, and the 256-byte tail that holds the count.
+constexpr int64_t STATIC_SORT_MAX_PAIRS = PDGS_SORT_STATIC_MAX_PAIRS;  // include/pdgs.h: 2^20
+constexpr size_t STATIC_SORT_TILES = (STATIC_SORT_MAX_PAIRS + SORT_THREADS * SORT_ITEMS_U64 - 1) / (SORT_THREADS * SORT_ITEMS_U64);
+constexpr size_t STATIC_SORT_BYTES = MAX_PASSES * RADIX * sizeof(uint32_t)                        // histograms
+                                     + 128                                                         // tickets
+                                     + MAX_PASSES * STATIC_SORT_TILES * RADIX * sizeof(uint32_t)   // look-back words
+                                     + 256;                                                        // pair count
+static __device__ __align__(256) unsigned char g_static_sort_scratch[STATIC_SORT_BYTES];  // ~2.7 MiB per GPU
+
+// In host code `g_static_sort_scratch` is only a handle the runtime knows the array by; the address a kernel can use
+// has to be asked for, per device, while that device is current.  Looked up once per device and kept.
+constexpr int STATIC_MAX_DEVICES = 64;
+static void* g_static_sort_ptr[STATIC_MAX_DEVICES] = {};
+static std::mutex g_static_sort_mutex;
+
+static int static_sort_scratch(void** out) {
+  int dev = -1;
+  PD_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES) return fail(PDGS_E_INVALID, "pdgs_sort_pairs_static: device ordinal out of range");
+  std::lock_guard<std::mutex> guard(g_static_sort_mutex);
+  if (!g_static_sort_ptr[dev]) {
+    void* p = nullptr;
+    PD_CUDA(cudaGetSymbolAddress(&p, g_static_sort_scratch));
+    if (!p) return fail(PDGS_E_CUDA, "pdgs_sort_pairs_static: cudaGetSymbolAddress returned NULL");
+    g_static_sort_ptr[dev] = p;
+  }
+  *out = g_static_sort_ptr[dev];
+  return PDGS_OK;
+}
 
 extern "C" {
 
@@ -503,6 +543,38 @@ int pdgs_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, ui
   PD_CUDA(cudaMemcpyAsync(cnt, &n32, 4, cudaMemcpyHostToDevice, s));
   if (npass % 2 == 0) {
     // input must sit in A (= out buffers) for an even number of passes: copy in -> out first
+    PD_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, s));
+    PD_CUDA(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+  }
+  PD_CUDA(launch_sort_u64(keys_out, vals_out, keys_in, vals_in, cnt, n, npass, end_bit, scratch, s));
+  return PDGS_OK;
+}
+
+// pdgs_sort_pairs for callers that cannot allocate: same kernels, same result, but the working memory is the
+// library's own fixed array (see g_static_sort_scratch above) instead of a caller buffer.  Nothing here, or below
+// it, calls cudaMalloc / cudaFree or any routine that allocates.  The first call on a device looks up the array's
+// device address (make that call before starting a stream capture); later calls only enqueue work.  All calls on
+// a device share the one array: it is cleared at the start of every sort (the memset inside sort_impl), and two
+// sorts that run on the GPU at the same time -- different streams, different host threads -- corrupt each other.
+int pdgs_sort_pairs_static(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int64_t n,
+                           int32_t end_bit, void* stream) {
+  if (n < 0 || end_bit < 1 || end_bit > 64) return fail(PDGS_E_INVALID, "pdgs_sort_pairs_static: bad n / end_bit");
+  if (n > STATIC_SORT_MAX_PAIRS)
+    return fail(PDGS_E_INVALID, "pdgs_sort_pairs_static: n exceeds the built-in scratch (limit %s pairs); "
+                                "use pdgs_sort_pairs with a caller-provided scratch", "1048576");
+  if (n == 0) return PDGS_OK;
+  if (!keys_in || !vals_in || !keys_out || !vals_out) return fail(PDGS_E_INVALID, "pdgs_sort_pairs_static: NULL buffer");
+  void* scratch = nullptr;
+  const int rc = static_sort_scratch(&scratch);
+  if (rc != PDGS_OK) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int npass = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
+  SortScratch sc = carve_sort_scratch(scratch, n, SORT_THREADS * SORT_ITEMS_U64);
+  if (sc.bytes + 256 > STATIC_SORT_BYTES) return fail(PDGS_E_INVALID, "pdgs_sort_pairs_static: scratch layout outgrew the array");
+  uint32_t* cnt = (uint32_t*)((char*)scratch + sc.bytes);
+  const uint32_t n32 = (uint32_t)n;
+  PD_CUDA(cudaMemcpyAsync(cnt, &n32, 4, cudaMemcpyHostToDevice, s));
+  if (npass % 2 == 0) {
     PD_CUDA(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, s));
     PD_CUDA(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
   }

@@ -94,6 +94,7 @@ SYMBOLS = {
     "pdgs_mark_visible": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp]),
     "pdgs_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "pdgs_sort_pairs": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int32, vp, C.c_size_t, vp]),
+    "pdgs_sort_pairs_static": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int32, vp]),
     "pdgs_state_view": (C.c_int, [C.POINTER(PdgsState), C.c_int64, C.c_int32, C.c_int32, C.POINTER(PdgsStateView)]),
 }
 
