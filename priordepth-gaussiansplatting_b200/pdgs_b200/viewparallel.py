@@ -184,7 +184,7 @@ class ViewParallelRasterizer:
         self._count_lock = threading.Lock()
         self._copy_stream = None
         self._color_grads = None
-        self._pre_images: Dict[int, tuple] = {}  # view index -> (host target tensor, staged upload) for the NEXT step
+        self._pre_images: Dict[int, tuple] = {}  # view index -> ((host target, prior, mask, alpha mask), staged upload) for the NEXT step
         # chunks along P of the deferred SH backward when its rows are all-reduced behind it (world > 1); PDGS_REDUCE_CHUNKS.
         # Measured on 8 x B200 (profiles/README.md r02h): 1 chunk 17.99 ms/step, 4 chunks 18.31 -- NCCL loses more on the
         # smaller messages (732 MB in one call 1.80 ms, in 4 calls 2.07 ms) than the 0.5 ms SH kernel can hide, so the
@@ -306,7 +306,10 @@ class ViewParallelRasterizer:
 
         prefetch_images: dict(targets=..., priors=..., masks=..., alpha_masks=...) of the NEXT step (pinned host tensors).
         Each lane uploads the images of the view it will start the next step with as soon as it has launched its last
-        view of this step, so the next step's first kernels do not wait for a 20 MB image to cross PCIe."""
+        view of this step, so the next step's first kernels do not wait for a 20 MB image to cross PCIe.  It must carry
+        EVERY per-view tensor the next step will pass (the same objects): a staged upload is used only when its target,
+        prior, mask and alpha mask are identical to the next step's arguments for that view, otherwise it is dropped
+        and the view is uploaded again."""
         if isinstance(gaussians, tuple):  # handle from stage_gaussians(): wait for the upload on the compute stream
             gaussians, ev = gaussians
             if ev is not None:
@@ -343,8 +346,12 @@ class ViewParallelRasterizer:
             scratch = self._scratch.setdefault(lane, {})
             pending = None
             if sub:
-                pre = self._pre_images.pop(sub[0][1], None)   # uploaded during the previous step?
-                if pre is not None and pre[0] is targets[sub[0][1]]:
+                i0 = sub[0][1]
+                pre = self._pre_images.pop(i0, None)   # uploaded during the previous step?
+                # the staged upload is taken only if it was made from exactly the host tensors this step passes for
+                # that view: target, prior, depth mask and alpha mask, each by identity (None matches only None)
+                now = (targets[i0],) + tuple(d.get(i0) if d is not None else None for d in (priors, masks, alpha_masks))
+                if pre is not None and all(a is b for a, b in zip(pre[0], now)):
                     pending = pre[1]
                 else:
                     pending = self._upload(sub[0][1], targets, priors, masks, alpha_masks)
@@ -366,8 +373,9 @@ class ViewParallelRasterizer:
             if prefetch_images is not None and sub:
                 i0, nt = sub[0][1], prefetch_images["targets"]
                 if i0 in nt:
-                    self._pre_images[i0] = (nt[i0], self._upload(i0, nt, prefetch_images.get("priors"),
-                                                                 prefetch_images.get("masks"), prefetch_images.get("alpha_masks")))
+                    others = tuple(prefetch_images.get(k) for k in ("priors", "masks", "alpha_masks"))
+                    src = (nt[i0],) + tuple(d.get(i0) if d is not None else None for d in others)
+                    self._pre_images[i0] = (src, self._upload(i0, nt, *others))
             return res
 
         if lanes == 1:

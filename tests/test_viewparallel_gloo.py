@@ -148,3 +148,39 @@ def test_two_ranks_allreduce_equals_single_process_sum():
 def test_cuda_backend_is_mandatory_without_injection():
     with pytest.raises(RuntimeError, match="no CPU path"):
         ViewParallelRasterizer(10, 16, "cpu")
+
+
+def test_prefetched_images_are_used_only_when_every_tensor_is_this_steps():
+    """prefetch_images hand-over: the upload staged during the previous step replaces this step's upload of a lane's
+    first view only if target, prior, mask and alpha mask are all the very tensors this step passes; otherwise the
+    step's own arguments win (a stale or incomplete prefetch must not drop the depth-prior term or the alpha mask)."""
+    seen = []
+
+    def backend(gaussians, view, target, prior, mask, w_depth, acc, loss_acc):
+        seen.append((target, prior, mask))
+        return dict(num_rendered=0, launches=0)
+
+    sc = scenes.make_config("C4", P=8, n_views=2, scale_image=0.02)
+    H, W = sc.views[0].image_height, sc.views[0].image_width
+    tg = {i: torch.rand(3, H, W) for i in range(2)}
+    pr = {i: torch.rand(1, H, W) for i in range(2)}
+    vp = ViewParallelRasterizer(sc.P, 16, "cpu", backend=backend)
+    # the prefetch names the targets only, the next step also passes priors: staged upload must be dropped
+    vp.step({}, sc.views, tg, prefetch_images=dict(targets=tg))
+    assert 0 in vp._pre_images
+    seen.clear()
+    vp.step({}, sc.views, tg, priors=pr)
+    assert seen[0][0] is tg[0] and seen[0][1] is pr[0]
+    assert not vp._pre_images
+    # a complete prefetch is taken
+    vp.step({}, sc.views, tg, priors=pr, prefetch_images=dict(targets=tg, priors=pr))
+    staged = vp._pre_images[0][1]
+    seen.clear()
+    vp.step({}, sc.views, tg, priors=pr)
+    assert seen[0][0] is staged[0][0] and seen[0][1] is staged[0][1] and seen[0][1] is pr[0]
+    # priors replaced since the prefetch: this step's tensors are used
+    vp.step({}, sc.views, tg, priors=pr, prefetch_images=dict(targets=tg, priors=pr))
+    pr2 = {i: torch.rand(1, H, W) for i in range(2)}
+    seen.clear()
+    vp.step({}, sc.views, tg, priors=pr2)
+    assert seen[0][1] is pr2[0]
