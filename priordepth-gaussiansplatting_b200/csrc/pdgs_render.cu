@@ -253,9 +253,11 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
     if (__all_sync(FULL, done)) continue;  // this warp's patch is finished; it only helps staging
     const int cnt = min((uint32_t)RT, range.y - base);
     const uint32_t pos0 = base - range.x;
-    // shared address of the record of the last entry blended / of the entry that ended the pixel in THIS batch (0 = none):
-    // one move inside the loop, the list position is formed from it once per batch
-    uint32_t hit_rec = 0, end_rec = 0;
+    // shared address of the record of the last entry blended / of the entry that ended the pixel in THIS batch: one move
+    // inside the loop, the list position is formed from it once per batch.  "None" is 0xffffffff, which no 16-byte
+    // aligned record address can be (0 could: nothing forbids the stage from starting at shared address 0).
+    constexpr uint32_t NO_REC = 0xffffffffu;
+    uint32_t hit_rec = NO_REC, end_rec = NO_REC;
     for (int k = 0; k * 32 < cnt; ++k) {
       // survivors of this warp's patch, bit-reversed so that the leading one is the first list entry
       uint32_t rm = __brev(__ballot_sync(FULL, (st.mask[k * 32 + lane] & wbit) != 0));
@@ -311,8 +313,8 @@ __global__ void __launch_bounds__(RT, PDGS_FWD_CTAS) render_forward_kernel(const
       }
       if (__all_sync(FULL, done)) break;
     }
-    if (hit_rec) last = pos0 + ((hit_rec - st_addr) >> 4) + 1u;
-    if (COUNT && end_rec) tested = pos0 + ((end_rec - st_addr) >> 4) + 1u;
+    if (hit_rec != NO_REC) last = pos0 + ((hit_rec - st_addr) >> 4) + 1u;
+    if (COUNT && end_rec != NO_REC) tested = pos0 + ((end_rec - st_addr) >> 4) + 1u;
   }
   if (inside) {
     const size_t pix = (size_t)py * W + px, hw = (size_t)W * H;

@@ -544,6 +544,7 @@ def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int, 
                 return t.cpu() if to_cpu else t
         raise L.PdgsError("state view pointer outside the state blobs")
 
+    counters = _work_counters_on(dev)
     R = int(num_rendered)
     point_list = grab(v.point_list, R, torch.int32)
     sorted_tiles = grab(v.sorted_tiles, R, torch.int32)
@@ -556,16 +557,24 @@ def state_view(geom, binning, image, P: int, W: int, H: int, num_rendered: int, 
     return dict(
         point_list=point_list, sorted_keys=sorted_keys, sorted_tiles=sorted_tiles,
         ranges=grab(v.ranges, tiles * 2, torch.int32).view(-1, 2), final_T=grab(v.final_T, W * H, torch.float32),
-        n_contrib=grab(v.n_contrib, W * H, torch.int32), n_tested=grab(v.n_tested, W * H, torch.int32),
-        n_accepted=grab(v.n_accepted, W * H, torch.int32), tiles_touched=grab(v.tiles_touched, P, torch.int32),
+        n_contrib=grab(v.n_contrib, W * H, torch.int32),
+        # written by the forward blend only while the work counters are on; otherwise the planes are uninitialised memory
+        n_tested=grab(v.n_tested, W * H, torch.int32) if counters else None,
+        n_accepted=grab(v.n_accepted, W * H, torch.int32) if counters else None,
+        tiles_touched=grab(v.tiles_touched, P, torch.int32),
         point_offsets=grab(v.point_offsets, P, torch.int32), depth_order=grab(v.depth_order, P, torch.int32),
         xy=grab(v.xy, P * 4, torch.float32).view(-1, 4), conic_opacity=conic_opacity, rgb=rgb, depth_bits=depth32)
 
 
 def image_counters(geom, binning, image, P: int, W: int, H: int) -> dict:
     """Sums over pixels of the forward blend's per-pixel counters, reduced on the device:
-    n_tested (list entries evaluated), n_accepted (entries blended), n_contrib (last contributing position)."""
+    n_tested (list entries evaluated), n_accepted (entries blended), n_contrib (last contributing position).
+    The first two exist only for a forward made while set_work_counters(device, True) was in effect on the calling
+    thread; without it the planes were never written, so this raises instead of summing uninitialised memory."""
     lib = L.lib()
+    if not _work_counters_on(image.device):
+        raise L.PdgsError("image_counters: the work counters are off for this thread's handle; call "
+                          "set_work_counters(device, True) before the forward whose counters you want")
     st = _state(geom, image, binning if binning.numel() else None, _binning_capacity(binning))
     v = L.PdgsStateView()
     L.check(lib.pdgs_state_view(C.byref(st), P, W, H, C.byref(v)), "pdgs_state_view")
@@ -588,6 +597,16 @@ def set_stage_timing(device, enable: bool) -> None:
             L.check(L.lib().pdgs_set_stage_timing(h, int(bool(enable))), "pdgs_set_stage_timing")
 
 
+_work_counters = {}  # (thread id, device index) -> work counters enabled on that thread's handle
+
+
+def _work_counters_on(device) -> bool:
+    import threading
+    dev = torch.device(device)
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    return bool(_work_counters.get((threading.get_ident(), int(idx))))
+
+
 def set_work_counters(device, enable: bool) -> None:
     """Turn the forward blend's per-pixel work counters (n_tested / n_accepted, read by image_counters / state_view) on
     or off for the CALLING thread's handle on `device`.  They are off by default (C ABI pdgs_set_work_counters)."""
@@ -595,6 +614,8 @@ def set_work_counters(device, enable: bool) -> None:
     with torch.cuda.device(dev):
         idx = dev.index if dev.index is not None else torch.cuda.current_device()
         L.check(L.lib().pdgs_set_work_counters(L.handle(idx), int(bool(enable))), "pdgs_set_work_counters")
+        import threading
+        _work_counters[(threading.get_ident(), int(idx))] = bool(enable)
 
 
 def stage_times(device) -> dict:

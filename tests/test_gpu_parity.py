@@ -339,6 +339,11 @@ def test_work_counters_match_the_oracle_counts():
     assert abs(c["n_accepted"] - res.n_acc) <= 2e-3 * res.n_acc
     assert abs(c["n_tested"] - res.n_test) <= 2e-3 * res.n_test
     assert abs(c["n_contrib"] - res.n_test_bwd) <= 2e-3 * res.n_test_bwd
+    # with the counters off the two planes are never written: asking for them raises / yields None, not garbage
+    with pytest.raises(Exception, match="work counters are off"):
+        rz.image_counters(geom, binning, img, sc.P, view.image_width, view.image_height)
+    sv = rz.state_view(geom, binning, img, sc.P, view.image_width, view.image_height, R)
+    assert sv["n_tested"] is None and sv["n_accepted"] is None and sv["n_contrib"].numel() == view.image_width * view.image_height
 
 
 def test_mark_visible():
@@ -401,3 +406,47 @@ def test_full_size_properties_c2():
     # culled Gaussians get exactly zero gradient rows
     culled = torch.from_numpy(st["radii"] == 0).to(DEV)
     assert float(lv["shs"].grad[culled].abs().max()) == 0.0 and float(lv["means3D"].grad[culled].abs().max()) == 0.0
+
+
+def test_first_slot_of_a_batch_is_the_only_contributor():
+    """The forward blend remembers the last blended list entry by the shared-memory address of its staged record; slot 0
+    of a 256-entry batch is the lowest such address, so "none" must not be encoded as a value that slot can take.
+    (a) one Gaussian: every covered pixel's only contributor is slot 0 of the first batch;
+    (b) 257 Gaussians in one tile, the farthest alone at its own spot: the pixels there see only list entry 256 = slot 0
+        of the SECOND batch.  n_contrib, image and gradients against the oracle."""
+    # (a)
+    sc = scenes.camera_relative_scene("s0", 5, 1, 32, 32, 3.0, behind_frac=0.0)
+    sc.means3D[:] = torch.tensor([[0.05, -0.05, 2.0]])
+    sc.scales[:] = torch.tensor([[0.05, 0.04, 0.05]])
+    sc.opacities[:] = 0.9
+    v = sc.views[0]
+    o, res, st = helpers.run_oracle(sc, v)
+    lv, color, radii, invd = helpers.run_cuda(sc, v, DEV)
+    sv = _check_ints(sc, v, lv, color, radii, st)
+    _check_images(res, color, invd, sv, v)
+    nc = sv["n_contrib"].view(v.image_height, v.image_width)
+    assert int(nc.max()) == 1 and int((nc == 1).sum()) >= 10
+    _check_grads(o, lv, color, invd)
+    assert float(lv["means3D"].grad.abs().max()) > 0
+    # (b)
+    P = 257
+    sc = scenes.camera_relative_scene("s1", 6, P, 16, 16, 1.0, behind_frac=0.0)
+    focal = 16 / (2.0 * 0.625)
+    z = 2.0 + 0.01 * torch.arange(P, dtype=torch.float32)
+    spot = torch.tensor([[-4.0, -4.0]]).repeat(P, 1)   # pixel offsets from the image centre
+    spot[P - 1] = torch.tensor([4.0, 4.0])             # the farthest Gaussian sits alone
+    sc.means3D[:] = torch.cat([spot * z[:, None] / focal, z[:, None]], dim=1)
+    sc.scales[:] = (z / focal)[:, None] * 0.6
+    sc.opacities[:] = 0.02                             # the stack stays far from saturating, so all 257 are listed
+    sc.opacities[P - 1] = 0.9
+    v = sc.views[0]
+    o, res, st = helpers.run_oracle(sc, v)
+    lv, color, radii, invd = helpers.run_cuda(sc, v, DEV)
+    sv = _check_ints(sc, v, lv, color, radii, st)
+    assert int(sv["ranges"].view(-1, 2)[0, 1]) == P and int(sv["point_list"][P - 1]) == P - 1
+    _check_images(res, color, invd, sv, v)
+    nc = sv["n_contrib"].view(16, 16)
+    assert int(nc[12, 12]) == P and int(res.n_contrib[12, 12]) == P     # the lone Gaussian's centre pixel
+    assert float(res.final_T[12, 12]) < 0.5
+    _check_grads(o, lv, color, invd)
+    assert float(lv["opacities"].grad[P - 1].abs()) > 0
