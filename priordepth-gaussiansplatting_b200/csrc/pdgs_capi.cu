@@ -189,6 +189,9 @@ static int make_args(const PdgsScene* sc, const PdgsCamera* cam, DeviceArgs& a) 
   if (!sc || !cam) return fail(PDGS_E_INVALID, "scene/camera is NULL");
   if (sc->P < 0) return fail(PDGS_E_INVALID, "P < 0");
   if (cam->image_width <= 0 || cam->image_height <= 0) return fail(PDGS_E_INVALID, "image size must be positive");
+  // the reference traps on a culled point when prefiltered is set and its caller always passes False
+  // (/root/reference/gaussian_renderer/__init__.py:47); refused here rather than silently ignored (include/pdgs.h)
+  if (cam->prefiltered) return fail(PDGS_E_INVALID, "prefiltered=1 is not supported (the reference's caller always passes False)");
   if (sc->P > 0) {
     if (!sc->means3D || !sc->opacities) return fail(PDGS_E_INVALID, "means3D/opacities is NULL");
     const bool split = sc->shs_dc != nullptr;

@@ -113,3 +113,55 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dp, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
                 assert "raster_oracle" not in src and "bitmodel" not in src, f
+
+
+def test_prefiltered_is_refused_at_the_c_abi(lib):
+    """include/pdgs.h (PdgsCamera.prefiltered): pdgs_forward / pdgs_backward return PDGS_E_INVALID for 1.  The flag is
+    checked on the host before any CUDA call, so dummy non-NULL pointers are enough and no GPU is needed."""
+    l = lib.lib()
+    d = ctypes.c_void_p(256)
+    cam = lib.PdgsCamera(image_height=16, image_width=16, tanfovx=0.5, tanfovy=0.5, bg=d, scale_modifier=1.0,
+                         viewmatrix=d, projmatrix=d, sh_degree=0, campos=d, prefiltered=1, debug=0, antialiasing=0)
+    sc = lib.PdgsScene(P=0, M=0)
+    st, out, grads = lib.PdgsState(), lib.PdgsForwardOut(), lib.PdgsGrads()
+    R = ctypes.c_int64(0)
+    rc = l.pdgs_forward(d, ctypes.byref(sc), ctypes.byref(cam), ctypes.byref(st), ctypes.byref(out), 0, ctypes.byref(R), None)
+    assert rc == lib.PDGS_E_INVALID and "prefiltered" in lib.last_error()
+    rc = l.pdgs_backward(d, ctypes.byref(sc), ctypes.byref(cam), ctypes.byref(st), d, 0, d, None, d, 0, ctypes.byref(grads), None)
+    assert rc == lib.PDGS_E_INVALID and "prefiltered" in lib.last_error()
+    cam.prefiltered = 0  # the same call gets past the flag (and then stops at the missing output buffers)
+    rc = l.pdgs_forward(d, ctypes.byref(sc), ctypes.byref(cam), ctypes.byref(st), ctypes.byref(out), 0, ctypes.byref(R), None)
+    assert rc == lib.PDGS_E_INVALID and "prefiltered" not in lib.last_error()
+
+
+def test_ctypes_structs_match_the_header_layout(lib, tmp_path):
+    """Sizes and field offsets of pdgs_b200/_lib.py's ctypes structures against what a C compiler makes of
+    include/pdgs.h (a struct that is short or shifted makes the library read past its end)."""
+    structs = {"PdgsCamera": lib.PdgsCamera, "PdgsScene": lib.PdgsScene, "PdgsState": lib.PdgsState,
+               "PdgsForwardOut": lib.PdgsForwardOut, "PdgsGrads": lib.PdgsGrads, "PdgsAdamGroup": lib.PdgsAdamGroup,
+               "PdgsStateView": lib.PdgsStateView}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{HEADER}"', 'int main(void) {']
+    for name, cls in structs.items():
+        lines.append(f'  printf("{name} size %zu\\n", sizeof({name}));')
+        for field, _ in cls._fields_:
+            lines.append(f'  printf("{name} {field} %zu\\n", offsetof({name}, {field}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c11", "-o", str(exe), str(src)], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout
+    seen = 0
+    for line in out.splitlines():
+        name, field, value = line.split()
+        cls = structs[name]
+        got = ctypes.sizeof(cls) if field == "size" else getattr(cls, field).offset
+        assert got == int(value), (name, field, got, value)
+        seen += 1
+    assert seen == sum(len(c._fields_) + 1 for c in structs.values())
+    # the header's field lists and the binding's agree in count too (offsetof above only sees the binding's names)
+    hdr = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
+    for name, cls in structs.items():
+        body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), hdr, flags=re.S).group(1)
+        n_fields = sum(len(decl.split(",")) for decl in body.split(";") if decl.strip())
+        assert n_fields == len(cls._fields_), (name, n_fields, len(cls._fields_))
