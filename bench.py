@@ -35,7 +35,7 @@ import torch  # noqa: E402
 
 METRIC = "fwd+bwd raster views/s @1.6K px, ~3M Gaussians (batch of 64 cameras, view-parallel)"
 UNIT = "views/s"
-SM_COUNT, FP32_LANES = 148, 128
+FP32_LANES = 128  # fp32 lanes per SM; the SM count is read from the device
 
 
 def parse_args():
@@ -386,16 +386,23 @@ def main():
         # positions, at most 12 in total so the arm ends within a few minutes; one warm pass per position
         per_pos = max(1, min(4, -(-max(1, args.steps) // 3)))
         base, t_sample = cpu_arm(args, scene, 3, per_pos, 1 if args.warmup > 0 else 0)
-        line = dict(impl="reference", metric=METRIC, value=base["value"], unit=UNIT, n_gpus=args.gpus, steps=args.steps,
-                    warmup=args.warmup, ms_per_step=1e3 * t_sample, steps_timed=3 * per_pos, higher_is_better=True,
+        # `steps` is what was timed (window samples), not what was asked for; `ms_per_step` describes the same quantity as
+        # `value` (one step = all views of the batch, extrapolated from the samples by pair count); the duration of one
+        # measured sample is kept apart as `ms_per_sample`
+        n_views = len(scene.views)
+        line = dict(impl="reference", metric=METRIC, value=base["value"], unit=UNIT, n_gpus=args.gpus, steps=3 * per_pos,
+                    steps_requested=args.steps, warmup=args.warmup,
+                    ms_per_step=(1e3 * n_views / base["value"]) if base["value"] > 0 else None,
+                    ms_per_sample=1e3 * t_sample, steps_timed=3 * per_pos, higher_is_better=True,
                     scaling="strong", vs_baseline=None, dtype="f64", data="synthetic", extrapolated=True,
                     config=workload_config(args, scene, world=max(1, args.gpus)), cpu_baseline=base,
                     e2e=dict(value=base["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                     gpu_launches=0, wall_s=time.perf_counter() - t0,
                     note="EXTRAPOLATED CPU-ORACLE SAMPLE, not a speed-up denominator: the reference rasterizer is CUDA-only and "
                          "its source is absent from the checkout (empty submodule), so this arm times the float64 CPU "
-                         "transcription of its maths (oracle/) on tile windows of one view (`ms_per_step` = one measured "
-                         "sample) and scales by pair count to views/s.  GPU-side denominators (CUB, the reference's "
+                         "transcription of its maths (oracle/) on tile windows of one view (`ms_per_sample` = one measured "
+                         "sample, `steps` = samples timed) and scales by pair count to views/s (`ms_per_step` = the "
+                         "extrapolated time of one batch of views).  GPU-side denominators (CUB, the reference's "
                          "fused-ssim kernel) are in the b200 arm's `library_baselines`.")
         print(json.dumps(line))
         return 0
@@ -616,7 +623,8 @@ def main():
 
     # ---------------- roofline per stage (rank 0's launches) ----------------
     peaks = measured_peaks()
-    fp32_peak = SM_COUNT * FP32_LANES * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s at the max SM clock
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count   # read from the device; B200: 148
+    fp32_peak = sm_count * FP32_LANES * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s at the max SM clock
     nv = max(work["views"], 1)
     Pn, V, R = work["P"], work["V"] / nv, work["R"] / nv
     T, HW = work["tiles"], work["HW"]
@@ -626,7 +634,8 @@ def main():
     # (u32, u32)", which yields the reference's sorted list from 8-byte instead of 12-byte pairs and 2 instead of 6
     # passes over R; SURVEY.md 8(d)'s figure for the reference's single 64-bit sort is 152 R.
     alg = {
-        "preprocess": ("hbm", 12 * Pn + 224 * V + 12 * Pn + 40 * V),
+        # SURVEY 8(d) / DESIGN.md section 4: read 12 P + 224 V, write 8 P (radii, tiles_touched) + 40 V = 20 P + 264 V
+        "preprocess": ("hbm", 12 * Pn + 224 * V + 8 * Pn + 40 * V),
         "depth_sort": ("hbm", 4 * Pn + 12 * Pn + 3 * 16 * Pn),
         "scan": ("hbm", 12 * Pn),
         # fused scan + duplicate: sorted order 4P, tile rects 8P gathered, point_offsets 4P written, 8-byte pairs written
@@ -665,9 +674,12 @@ def main():
     roofline = None
     if top:
         roofline = dict(kernel=top["stage"], bound=top["bound"], achieved=top["achieved"], peak=top["peak"], unit=top["unit"],
-                        frac=top["frac"], traffic=top["traffic"], avg_ms=top["avg_ms"], share_of_step=top["share"],
+                        frac=top["frac"], traffic=top["traffic"],
+                        traffic_source=dict(file=traffic.get("_file") or str(traffic.get("_source", "")).split(":")[0] or None,
+                                            commit=traffic.get("_commit")),
+                        avg_ms=top["avg_ms"], share_of_step=top["share"],
                         peak_source=("MEASURED_PEAKS.json hbm_gbs (%s)" % peaks["source"]) if top["bound"] == "hbm" else
-                        "derived: 148 SMs x 128 fp32 lanes x 2 x sm_max_mhz (MEASURED_PEAKS.json has no fp32 SIMT figure)")
+                        "derived: %d SMs (device attribute) x 128 fp32 lanes x 2 x sm_max_mhz (MEASURED_PEAKS.json has no fp32 SIMT figure)" % sm_count)
 
     lib = None
     if not args.no_library_baselines:

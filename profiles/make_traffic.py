@@ -46,6 +46,13 @@ for name, b in launches:
         break
 doc = {"_source": "%s: dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, one C4 view (3M Gaussians, "
                   "1600x1064); multi-kernel stages are summed over their kernels (profiles/make_traffic.py)" % src}
+try:  # the commit the capture was taken at (the working tree's HEAD when this script runs right after the capture)
+    import subprocess
+    doc["_commit"] = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True,
+                                    cwd=os.path.dirname(os.path.abspath(__file__))).stdout.strip() or None
+except OSError:
+    doc["_commit"] = None
+doc["_file"] = os.path.basename(src)
 doc.update(out)
 json.dump(doc, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "traffic.json"), "w"), indent=1)
 print(json.dumps(doc, indent=1))
