@@ -332,13 +332,18 @@ def library_baselines(scene, view_settings, g_dev, dev, H, W, P):
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, H, W, g_dev["shs"], rs.sh_degree, rs.campos, False,
                 False, False)
         sv = rz.state_view(geom, binning, img, P, W, H, R, to_cpu=False)
-        ku, vu = gb.reference_binning_inputs(sv)
+        chain_t = dict(warmup=5, iters=30)
+        ku, vu = gb.reference_binning_chain(sv, radii, W, H, timing=chain_t)
         T = ((W + 15) // 16) * ((H + 15) // 16)
         c = gb.cub_binning(sv["tiles_touched"], ku, vu, T, warmup=5, iters=30)
         out["cub"] = dict(
-            what="reference K2 + K4 library calls on this view's arrays: cub::DeviceScan::InclusiveSum(tiles_touched[P]) and "
+            what="reference-shaped K2 + K3 + K4 on this view's K1 outputs (xy, radii, depth bits, tiles_touched; nothing of the "
+                 "new pipeline's binning is read): cub::DeviceScan::InclusiveSum(tiles_touched[P]), duplicateWithKeys with one "
+                 "thread per Gaussian in index order (tools/cub_baseline.cu, SURVEY A.6) and "
                  "cub::DeviceRadixSort::SortPairs(u64 tile<<32|depth, u32 id) over bits [0, 32+bits(T)); CUDA 12.9 CUB",
-            P=P, R=int(R), end_bit=c["end_bit"], scan_ms=c["scan_ms"], sort_pairs_u64_ms=c["sort_ms"],
+            P=P, R=int(R), end_bit=c["end_bit"], scan_ms=c["scan_ms"], duplicate_ref_shaped_ms=chain_t["duplicate_ms"],
+            sort_pairs_u64_ms=c["sort_ms"],
+            reference_k2_k3_k4_ms=c["scan_ms"]["median"] + chain_t["duplicate_ms"]["median"] + c["sort_ms"]["median"],
             sorted_list_equals_ours=bool(torch.equal(c["sorted_vals"], sv["point_list"]) and
                                          torch.equal(c["sorted_keys"], sv["sorted_keys"])))
         del sv, ku, vu, c
@@ -698,6 +703,7 @@ def main():
             cubr["ours_ms"] = dict(depth_sort=t.get("depth_sort"), scan_duplicate=t.get("duplicate"), tile_sort=t.get("sort"))
             cubr["ours_sorts_ms"] = (t.get("depth_sort") or 0.0) + (t.get("sort") or 0.0)
             cubr["reference_sort_plus_scan_ms"] = cubr["sort_pairs_u64_ms"]["median"] + cubr["scan_ms"]["median"]
+            cubr["ours_k2_k3_k4_ms"] = cubr["ours_sorts_ms"] + (t.get("duplicate") or 0.0) + (t.get("scan") or 0.0)
         fs = lib.get("fused_ssim", {})
         if "loss" in t and fs.get("reference_ms"):
             fs["note"] = ("pdgs_image_loss_ssim = value + cotangent of (1-l)*L1 + l*(1-SSIM) on the raw render (clamp inside), "

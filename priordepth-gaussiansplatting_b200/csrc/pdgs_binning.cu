@@ -689,7 +689,7 @@ static cudaError_t sort_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint3
   // count, sets the cost of small inputs: PDGS_HIST_CTAS_PER_SM blocks per SM at most
   static const int hist_per_sm = [] { const char* e = getenv("PDGS_HIST_CTAS_PER_SM"); return e ? atoi(e) : 4; }();
   int hist_blocks = (int)((capacity + 256 * 16 - 1) / (256 * 16));
-  if (hist_blocks > 148 * hist_per_sm) hist_blocks = 148 * hist_per_sm;
+  if (hist_blocks > sm_count() * hist_per_sm) hist_blocks = sm_count() * hist_per_sm;
   if (hist_blocks < 1) hist_blocks = 1;
   sort_histogram_kernel<KeyT><<<hist_blocks, 256, 0, s>>>(kin, n_dev, n_host, capacity, npass, end_bit, sc.hist);
   e = cudaGetLastError();
@@ -728,7 +728,7 @@ cudaError_t launch_ranges(const uint32_t* tkeys, const uint32_t* n_dev, int64_t 
   if (e != cudaSuccess) return e;
   if (capacity <= 0) return cudaSuccess;
   int blocks = (int)((capacity + 255) / 256);
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks > sm_count() * 16) blocks = sm_count() * 16;
   ranges_kernel<<<blocks, 256, 0, s>>>(tkeys, n_dev, capacity, ranges);
   return cudaGetLastError();
 }

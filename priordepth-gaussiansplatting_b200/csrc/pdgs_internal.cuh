@@ -43,6 +43,19 @@ static_assert(sizeof(Ctrl) == 256, "Ctrl must be 256 bytes");
 
 inline __host__ __device__ size_t align_up(size_t v, size_t a = 128) { return (v + a - 1) / a * a; }
 
+// Number of SMs of the current device (grid sizing of the persistent / capped launches); asked once per device.
+inline __host__ int sm_count() {
+  static int cached[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;  // B200
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
 struct GeomView {
   Ctrl* ctrl;
   float4* gA;               // (x, y, conic.x, conic.y)

@@ -110,7 +110,7 @@ cudaError_t launch_image_loss(const float* color, const float* target, const flo
                          ? 1
                          : 0;
   size_t blocks = ((n_color ? n_color : n_depth) / 4 + LOSS_THREADS - 1) / LOSS_THREADS;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > sm_count() * 8) blocks = sm_count() * 8;
   if (blocks < 1) blocks = 1;
   image_loss_kernel<<<(unsigned)blocks, LOSS_THREADS, 0, s>>>(color, target, invdepth, prior, mask, alpha, clamp01, n_color,
                                                               n_depth, gc, gd, dL_dcolor, dL_dinvdepth, loss, vec_ok);

@@ -875,11 +875,11 @@ cudaError_t launch_preprocess_backward(const DeviceArgs& a, GeomView g, const in
     const int64_t ntiles = (a.P + PB_TILE - 1) / PB_TILE;
     if (gp.color_grad_view) {  // SH backward deferred to launch_sh_backward_views: only the accumulator block is staged
       const int bulk_ok = al16(acc);
-      const unsigned blocks = (unsigned)(ntiles < PDGS_PB_DEFER_CTAS * 148 ? ntiles : PDGS_PB_DEFER_CTAS * 148);
+      const unsigned blocks = (unsigned)(ntiles < PDGS_PB_DEFER_CTAS * sm_count() ? ntiles : PDGS_PB_DEFER_CTAS * sm_count());
       preprocess_backward_sh_kernel<true, false><<<blocks, PB_TILE, offsetof(PbShared, sh_in), s>>>(a, g, radii, acc, gp, bulk_ok);
       return cudaGetLastError();
     }
-    const unsigned blocks = (unsigned)(ntiles < 2 * 148 ? ntiles : 2 * 148);  // persistent: two CTAs per SM
+    const unsigned blocks = (unsigned)(ntiles < 2 * sm_count() ? ntiles : 2 * sm_count());  // persistent: two CTAs per SM
     if (a.shs_dc) {
       if (gp.shs_dc && a.M > 1 && !gp.shs_rest) return cudaErrorInvalidValue;
       const int bulk_ok = al16(a.shs_dc) && (!a.shs_rest || al16(a.shs_rest)) && al16(acc) && (!gp.shs_dc || al16(gp.shs_dc)) &&

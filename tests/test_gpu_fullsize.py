@@ -60,7 +60,8 @@ def _check_integers(sc, view, st, R, radii, state, with_bitmodel_sort):
     assert torch.equal(sv["depth_bits"][vis].cpu(),
                        torch.from_numpy(st["depth_bits"].view(np.int32))[vis.cpu()])
     # the reference's K2 + K4 as library calls on the reference-format arrays
-    ku, vu = gb.reference_binning_inputs(sv)
+    # (K2 + reference-shaped K3 from K1's outputs only, then K4: nothing here reads the binning under test)
+    ku, vu = gb.reference_binning_chain(sv, radii, W, H)
     cub = gb.cub_binning(sv["tiles_touched"], ku, vu, T, warmup=1, iters=3)
     assert cub["scan_total"] == R                                   # cub::DeviceScan::InclusiveSum(tiles_touched)[-1]
     assert torch.equal(cub["sorted_vals"], sv["point_list"])        # cub::DeviceRadixSort::SortPairs == our sorted list

@@ -104,7 +104,7 @@ def test_sorted_list_equals_cub_sort_of_reference_keys(cfg):
     geom, binning, img = fn.saved_tensors[8], fn.saved_tensors[9], fn.saved_tensors[10]
     binning._pdgs_capacity = fn.binning_capacity
     sv = rz.state_view(geom, binning, img, sc.P, W, H, fn.num_rendered, to_cpu=False)
-    ku, vu = gb.reference_binning_inputs(sv)
+    ku, vu = gb.reference_binning_chain(sv, radii, W, H)   # from K1 outputs only, not from the sorted list under test
     # the unsorted pairs really are in the reference's duplicateWithKeys order: ids ascending, tiles ascending within an id
     assert bool((vu[1:] >= vu[:-1]).all())
     same = vu[1:] == vu[:-1]

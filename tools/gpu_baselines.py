@@ -35,6 +35,7 @@ def cub():
             getattr(l, name).argtypes = [C.c_int64, C.c_int]
         for name in ("cubb_sort_pairs_u64", "cubb_sort_pairs_u32"):
             getattr(l, name).argtypes = [vp, vp, vp, vp, C.c_int64, C.c_int, vp, C.c_size_t, vp]
+        l.cubb_duplicate_with_keys.argtypes = [vp, vp, vp, vp, vp, C.c_int64, C.c_int, C.c_int, vp, vp, vp, vp]
         _cub = l
     return _cub
 
@@ -63,12 +64,36 @@ def key_bits(tiles: int) -> int:
     return 32 + max(1, int(tiles).bit_length())
 
 
-def reference_binning_inputs(sv: dict):
-    """(keys_unsorted int64 [R], values_unsorted int32 [R]) exactly as the reference's duplicateWithKeys emits them
-    (Gaussians in index order, each one's tiles row-major = ascending tile id), rebuilt from a device-side
-    state view (rasterizer.state_view(..., to_cpu=False)) of the new pipeline's sorted list."""
-    order = torch.sort(sv["point_list"].to(torch.int64), stable=True).indices   # sorted list is tile-major: stable by id
-    return sv["sorted_keys"][order].contiguous(), sv["point_list"][order].contiguous()
+def reference_binning_chain(sv: dict, radii: torch.Tensor, W: int, H: int, timing: dict = None):
+    """(keys_unsorted int64 [R], values_unsorted int32 [R]) as the reference's K2 + K3 emit them, computed WITHOUT any output
+    of the new pipeline's binning: cub::DeviceScan::InclusiveSum over tiles_touched, then a reference-shaped
+    duplicateWithKeys (tools/cub_baseline.cu: one thread per Gaussian in index order, rectangle recomputed from the pixel
+    centre and radius, y outer / x inner, key = tile << 32 | depth bits).  Inputs are K1 outputs only:
+    sv["xy"], sv["depth_bits"], sv["tiles_touched"] (device-side state view) and the radii the forward returned.
+    timing: optional dict; receives duplicate_ms (median / p10 / p90 of the K3 kernel alone)."""
+    l = cub()
+    assert l is not None, "tools/libcub_baseline.so missing (make -C tools)"
+    tt, xy, db = sv["tiles_touched"].contiguous(), sv["xy"].contiguous(), sv["depth_bits"].contiguous()
+    dev = tt.device
+    assert xy.is_cuda and radii.device == dev and xy.shape[1] == 4
+    P = tt.numel()
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    tb = l.cubb_scan_temp_bytes(P)
+    temp = torch.empty(max(tb, 1), dtype=torch.uint8, device=dev)
+    offs = torch.empty_like(tt)
+    assert l.cubb_inclusive_sum_u32(_p(tt), _p(offs), P, _p(temp), tb, stream) == 0
+    R = int(offs[-1].item()) if P else 0
+    keys = torch.empty(R, dtype=torch.int64, device=dev)
+    vals = torch.empty(R, dtype=torch.int32, device=dev)
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+    rad = radii.to(torch.int32).contiguous()
+    dup = lambda: l.cubb_duplicate_with_keys(_p(xy), _p(rad), _p(db), _p(offs), _p(tt), P, (W + 15) // 16, (H + 15) // 16,
+                                             _p(keys), _p(vals), _p(err), stream)
+    assert dup() == 0
+    if timing is not None:  # the reference-shaped K3 timed alone (it rewrites the same pairs every time)
+        timing["duplicate_ms"] = _time(dup, timing.get("warmup", 3), timing.get("iters", 20))
+    assert int(err.item()) == 0, "tiles_touched disagrees with the rectangle recomputed from (xy, radius)"
+    return keys, vals
 
 
 def cub_binning(tiles_touched: torch.Tensor, keys_unsorted: torch.Tensor, vals_unsorted: torch.Tensor, tiles: int,
